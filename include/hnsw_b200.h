@@ -1,0 +1,175 @@
+/* hnsw_b200.h -- C ABI of the B200-native batched HNSW query engine for the
+ * binary-sketch path of JonasUJ/hnsw-itu (1024-bit sketches, Hamming distance).
+ *
+ * This header is the drop-in boundary: plain pointers and sizes, no C++ or
+ * torch types.  Each entry point names the reference interface it replaces
+ * (paths relative to the reference checkout).  The reference is Rust with no
+ * FFI today; INTEGRATION.md shows the `-sys` binding a maintainer would add.
+ *
+ * Conventions
+ *   - a sketch is 16 little-endian uint64 words = 128 bytes (cli/src/sketch.rs:7-10);
+ *     `queries` / `data` arrays are row-major (n, 16) uint64.
+ *   - keys are 0-based node indices as in the .idx file (the CLI adds +1 only
+ *     when writing HDF5, cli/src/main.rs:277,745).
+ *   - results are ordered by the reference's total order (distance, key)
+ *     (src/index/mod.rs:90-97).
+ *   - neighbour iteration order is the order ids appear in the .idx file
+ *     (the reference's own order is re-randomised per process).
+ *   - every function returns an hb_status; hb_last_error() gives a
+ *     thread-local message.  No exception or abort crosses this boundary.
+ *   - there is no CPU fallback: without a CUDA device every compute entry
+ *     point fails with HB_ERR_NO_DEVICE.
+ */
+#ifndef HNSW_B200_H_
+#define HNSW_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HB_VERSION 100 /* 0.1.0 */
+#define HB_SKETCH_WORDS 16
+
+typedef enum hb_status {
+  HB_OK = 0,
+  HB_ERR_INVALID = 1,      /* bad argument */
+  HB_ERR_IO = 2,           /* file could not be opened / short read or write */
+  HB_ERR_FORMAT = 3,       /* .idx bytes or graph arrays are inconsistent */
+  HB_ERR_CUDA = 4,         /* CUDA runtime error (message has the detail) */
+  HB_ERR_NO_DEVICE = 5,    /* no usable CUDA device: there is no CPU fallback */
+  HB_ERR_OOM = 6,          /* host or device allocation failed */
+  HB_ERR_EMPTY_RESULT = 7, /* padding requested but a search found nothing (the reference panics, main.rs:472) */
+  HB_ERR_UNSUPPORTED = 8,  /* e.g. ef above HB_MAX_EF */
+  HB_ERR_INTERNAL = 9
+} hb_status;
+
+/* Indexes<P> variants, same numbering as the bincode enum tag (cli/src/main.rs:441-446) */
+typedef enum hb_algo { HB_ALGO_BRUTEFORCE = 0, HB_ALGO_NSW = 1, HB_ALGO_HNSW = 2 } hb_algo;
+
+/* flags for hb_knns / hb_search */
+#define HB_PAD_LIKE_CLI 1u /* Indexes::search: repeat the first result up to k (main.rs:467-474) */
+
+#define HB_MAX_EF 4096u
+#define HB_MAX_K 4096u
+
+typedef struct hb_index hb_index; /* opaque: device-resident index + optional host copy */
+
+typedef struct hb_index_info {
+  int32_t algo;        /* hb_algo */
+  int32_t device;      /* CUDA ordinal the index lives on */
+  uint32_t n_graphs;   /* 0 bruteforce, 1 NSW, 1 + layers for HNSW (graph 0 = base) */
+  uint32_t row_stride; /* 32-bit words per adjacency row in HBM (word 0 = degree) */
+  uint64_t size;       /* Index::size(): number of base points */
+  uint64_t n_nodes_total;
+  uint64_t n_edges_total; /* directed */
+  int64_t entry_point;    /* as stored in the file (index into the top graph), -1 = None */
+  uint64_t device_bytes;
+} hb_index_info;
+
+/* per-query work counters (feature `instrument` of the reference traces V as
+ * "visited", src/index/nsw.rs:180-181; X/E/A complete the roofline byte model) */
+typedef struct hb_counters {
+  uint32_t expansions;   /* X: candidates expanded */
+  uint32_t ids_scanned;  /* E: neighbour ids iterated */
+  uint32_t dist_evals;   /* V: distance evaluations == |visited| */
+  uint32_t accepted;     /* A: pushes into the beam */
+} hb_counters;
+
+const char* hb_last_error(void);
+int hb_version(void);
+int hb_device_count(int* count);
+
+/* ---- index life cycle ------------------------------------------------- */
+
+/* read_index (cli/src/main.rs:224-234): parse a bincode 1.3.3 IndexFile<Sketch>
+ * and place it in HBM of `device`.  keep_host != 0 retains the host copy needed
+ * by hb_index_save_idx / hb_index_graph_export. */
+int hb_index_load_idx(const char* path, int device, int keep_host, hb_index** out);
+
+/* Build an index handle from arrays (what a Rust wrapper holding an
+ * `HNSW<Sketch>` would pass: hnsw.rs:255-271 `layers()`/`base()`).
+ * Graph 0 is the base, graph g>0 is layers[g-1].  For each graph:
+ * sketches (n,16) u64, down n u64 (index into the graph below; ignored for
+ * graph 0), off n+1 u64 CSR offsets, ids u32 or u64 (id_bytes = 4 | 8) in
+ * canonical neighbour order.  entry_point indexes the top graph, -1 = None. */
+int hb_index_from_parts(int algo, uint32_t n_graphs, const uint64_t* n_nodes, const uint64_t* const* sketches,
+                        const uint64_t* const* down, const uint64_t* const* off, const void* const* ids, int id_bytes,
+                        int64_t entry_point, int device, int keep_host, hb_index** out);
+
+/* write_index (main.rs:236-248): needs keep_host. */
+int hb_index_save_idx(const hb_index* idx, const char* path);
+/* ResultAttrs carried by the .idx (main.rs:311-320); params is "index=(efc=..,m=..,M=..)" */
+int hb_index_set_attrs(hb_index* idx, double buildtime, const char* params);
+void hb_index_free(hb_index* idx);
+uint64_t hb_index_size(const hb_index* idx); /* Index::size (src/index/mod.rs:22) */
+int hb_index_get_info(const hb_index* idx, hb_index_info* info);
+/* host copy of one graph (needs keep_host); any pointer may be NULL.  ids are returned as u64. */
+int hb_index_graph_dims(const hb_index* idx, uint32_t graph, uint64_t* n_nodes, uint64_t* n_edges);
+int hb_index_graph_export(const hb_index* idx, uint32_t graph, uint64_t* sketches, uint64_t* down, uint64_t* off, uint64_t* ids);
+
+/* ---- queries ------------------------------------------------------------ */
+
+/* Index::knns (src/index/mod.rs:28-42) through Indexes::search
+ * (cli/src/main.rs:457-477): one batched launch, results in input order.
+ * HOST buffers; H2D/D2H copies happen inside.  keys/dists are (nq, k) u64,
+ * found (nq) u32 = results before padding (<= min(k, ef)); rows are
+ * zero-filled past found[i] unless HB_PAD_LIKE_CLI.  counters may be NULL. */
+int hb_knns(const hb_index* idx, const uint64_t* queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags,
+            uint64_t* keys, uint64_t* dists, uint32_t* found, hb_counters* counters);
+
+/* Index::search (src/index/mod.rs:23): a batch of one. */
+int hb_search(const hb_index* idx, const uint64_t* query, uint32_t k, uint32_t ef, uint32_t flags, uint64_t* keys,
+              uint64_t* dists, uint32_t* found);
+
+/* Same with DEVICE buffers on the index's device; `stream` is a cudaStream_t
+ * (NULL = default stream).  Synchronises `stream` before returning (the
+ * exact-visited-set overflow check needs one word back from the device). */
+int hb_knns_device(const hb_index* idx, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags,
+                   void* d_keys, void* d_dists, void* d_found, void* d_counters, void* stream);
+
+/* ---- brute force / ground truth ----------------------------------------------- */
+
+/* `ground-truth` (cli/src/main.rs:715-754): Bruteforce::search
+ * (src/index/bruteforce.rs:37-47, MinK src/collections/mod.rs:52-77) for every
+ * query followed by the CLI's sort: the exact k smallest (distance, key),
+ * ascending.  HOST buffers; keys/dists (nq, k) u64.  n < k pads with
+ * (distance, key) = (UINT64_MAX, UINT64_MAX). */
+int hb_ground_truth(const uint64_t* data, uint64_t n, const uint64_t* queries, uint64_t nq, uint32_t k, int device,
+                    uint64_t* keys, uint64_t* dists);
+
+/* DEVICE buffers: d_data (n,16) u64 is one shard whose first row has global
+ * key `key_offset`; writes (nq, k) packed u64 = (distance << 32) | key,
+ * ascending; missing entries are UINT64_MAX. */
+int hb_ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq,
+                           uint32_t k, void* d_packed, void* stream);
+
+/* Exact (distance, key) merge of n_lists per-shard lists laid out
+ * (n_lists, nq, k) packed u64 -> (nq, k) packed (new for sharding; the order
+ * is total so the merge equals a global Bruteforce + sort). */
+int hb_topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_packed_out, void* stream);
+/* packed (nq,k) -> keys, dists u64 (UINT64_MAX entries stay UINT64_MAX in both) */
+int hb_unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists, void* stream);
+
+/* ---- synthetic sketches (bench/test input; integer-exact SimHash mixture) ---- */
+typedef struct hb_synth_params {
+  uint64_t seed_planes, seed_centres, seed_rows;
+  uint32_t latent_dim, n_clusters, centre_scale, noise_scale, distinct_planes;
+} hb_synth_params;
+int hb_synth_device(const hb_synth_params* p, uint64_t start_row, uint64_t n_rows, void* d_out, void* stream);
+
+/* ---- index construction (HNSWBuilder::extend_parallel, src/index/hnsw.rs:44-169) ---- */
+typedef struct hb_build_params {
+  uint32_t ef_construction; /* -c, default 96 (main.rs:519-521) */
+  uint32_t connections;     /* -m, default 24 */
+  uint32_t max_connections; /* -M, default 256 */
+  uint32_t rayon_threads;   /* stands in for rayon::current_num_threads(): chunk = 32 * this, and it is mixed into the level seed */
+} hb_build_params;
+int hb_build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params* p, int device, int keep_host, hb_index** out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HNSW_B200_H_ */
