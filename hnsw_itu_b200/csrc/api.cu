@@ -1,0 +1,323 @@
+// api.cu -- the extern "C" surface declared in include/hnsw_b200.h.
+// Every entry point converts exceptions into hb_status codes + a thread-local
+// message; nothing throws across the boundary.
+#include <cstring>
+#include <memory>
+
+#include "hb_internal.h"
+
+namespace hb {
+namespace {
+thread_local std::string g_last_error;
+}
+void set_last_error(const std::string& m) { g_last_error = m; }
+
+namespace {
+
+template <class F>
+int guarded(F&& f) {
+  try {
+    f();
+    return HB_OK;
+  } catch (const Error& e) {
+    g_last_error = e.what();
+    return e.code;
+  } catch (const std::bad_alloc&) {
+    g_last_error = "host allocation failed";
+    return HB_ERR_OOM;
+  } catch (const std::exception& e) {
+    g_last_error = e.what();
+    return HB_ERR_INTERNAL;
+  } catch (...) {
+    g_last_error = "unknown error";
+    return HB_ERR_INTERNAL;
+  }
+}
+
+template <class T>
+struct DevMem {
+  T* p = nullptr;
+  explicit DevMem(size_t n) { HB_CUDA(cudaMalloc(&p, (n ? n : 1) * sizeof(T))); }
+  ~DevMem() { cudaFree(p); }
+  DevMem(const DevMem&) = delete;
+  DevMem& operator=(const DevMem&) = delete;
+};
+
+Index* as_index(const hb_index* h) {
+  HB_REQUIRE(h != nullptr, HB_ERR_INVALID, "null index handle");
+  return reinterpret_cast<Index*>(const_cast<hb_index*>(h));
+}
+
+}  // namespace
+}  // namespace hb
+
+using namespace hb;
+
+extern "C" {
+
+const char* hb_last_error(void) { return g_last_error.c_str(); }
+int hb_version(void) { return HB_VERSION; }
+
+int hb_device_count(int* count) {
+  return guarded([&] {
+    HB_REQUIRE(count != nullptr, HB_ERR_INVALID, "null argument");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      n = 0;
+    }
+    *count = n;
+  });
+}
+
+int hb_index_load_idx(const char* path, int device, int keep_host, hb_index** out) {
+  return guarded([&] {
+    HB_REQUIRE(path && out, HB_ERR_INVALID, "null argument");
+    *out = nullptr;
+    ensure_device(device);  // fail before parsing gigabytes when there is no GPU
+    Attrs attrs;
+    int algo = 0;
+    int64_t ep = -1;
+    std::vector<HostGraph> graphs;
+    read_idx_file(path, attrs, algo, graphs, ep);
+    Index* idx = index_from_host(algo, std::move(graphs), ep, device, keep_host != 0);
+    const uint64_t size = idx->attrs.size;
+    idx->attrs = attrs;
+    idx->attrs.size = attrs.size ? attrs.size : size;
+    *out = reinterpret_cast<hb_index*>(idx);
+  });
+}
+
+int hb_index_from_parts(int algo, uint32_t n_graphs, const uint64_t* n_nodes, const uint64_t* const* sketches,
+                        const uint64_t* const* down, const uint64_t* const* off, const void* const* ids, int id_bytes,
+                        int64_t entry_point, int device, int keep_host, hb_index** out) {
+  return guarded([&] {
+    HB_REQUIRE(out && n_nodes && sketches, HB_ERR_INVALID, "null argument");
+    *out = nullptr;
+    HB_REQUIRE(n_graphs >= 1 && n_graphs <= 64, HB_ERR_INVALID, "n_graphs out of range");
+    HB_REQUIRE(id_bytes == 4 || id_bytes == 8, HB_ERR_INVALID, "id_bytes must be 4 or 8");
+    ensure_device(device);
+    std::vector<HostGraph> graphs(n_graphs);
+    for (uint32_t g = 0; g < n_graphs; ++g) {
+      HostGraph& hg = graphs[g];
+      hg.n = n_nodes[g];
+      HB_REQUIRE(hg.n <= 0xFFFFFFFEull, HB_ERR_UNSUPPORTED, "more than 2^32-2 nodes in one graph");
+      HB_REQUIRE(hg.n == 0 || sketches[g], HB_ERR_INVALID, "null sketch array");
+      hg.sk.assign(sketches[g], sketches[g] + hg.n * 16);
+      if (algo == HB_ALGO_BRUTEFORCE) {
+        hg.off.assign(hg.n + 1, 0);
+        continue;
+      }
+      HB_REQUIRE(off && off[g] && ids, HB_ERR_INVALID, "null adjacency arrays");
+      hg.off.assign(off[g], off[g] + hg.n + 1);
+      const uint64_t ne = hg.off[hg.n];
+      HB_REQUIRE(ne == 0 || ids[g], HB_ERR_INVALID, "null id array");
+      hg.ids.resize(ne);
+      if (id_bytes == 4) {
+        std::memcpy(hg.ids.data(), ids[g], ne * 4);
+      } else {
+        const uint64_t* wide = static_cast<const uint64_t*>(ids[g]);
+        for (uint64_t j = 0; j < ne; ++j) {
+          HB_REQUIRE(wide[j] < hg.n, HB_ERR_FORMAT, "neighbour id out of range");
+          hg.ids[j] = (uint32_t)wide[j];
+        }
+      }
+      if (g > 0) {
+        HB_REQUIRE(down && down[g], HB_ERR_INVALID, "null down-link array");
+        hg.down.assign(down[g], down[g] + hg.n);
+      }
+    }
+    *out = reinterpret_cast<hb_index*>(index_from_host(algo, std::move(graphs), entry_point, device, keep_host != 0));
+  });
+}
+
+int hb_index_save_idx(const hb_index* h, const char* path) {
+  return guarded([&] {
+    Index* idx = as_index(h);
+    HB_REQUIRE(path, HB_ERR_INVALID, "null path");
+    HB_REQUIRE(idx->has_host, HB_ERR_INVALID, "index was created without keep_host; nothing to serialise");
+    write_idx_file(path, idx->attrs, idx->algo, idx->host, idx->ep_file);
+  });
+}
+
+int hb_index_set_attrs(hb_index* h, double buildtime, const char* params) {
+  return guarded([&] {
+    Index* idx = as_index(h);
+    idx->attrs.buildtime = buildtime;
+    if (params) idx->attrs.params = params;
+  });
+}
+
+void hb_index_free(hb_index* h) { delete reinterpret_cast<Index*>(h); }
+
+uint64_t hb_index_size(const hb_index* h) { return h ? reinterpret_cast<const Index*>(h)->n_base : 0; }
+
+int hb_index_get_info(const hb_index* h, hb_index_info* info) {
+  return guarded([&] {
+    Index* idx = as_index(h);
+    HB_REQUIRE(info, HB_ERR_INVALID, "null argument");
+    info->algo = idx->algo;
+    info->device = idx->device;
+    info->n_graphs = idx->algo == HB_ALGO_BRUTEFORCE ? 0u : (uint32_t)idx->g_nodes.size();
+    info->row_stride = idx->stride;
+    info->size = idx->n_base;
+    info->n_nodes_total = idx->n_total;
+    uint64_t e = 0;
+    for (uint64_t x : idx->g_edges) e += x;
+    info->n_edges_total = e;
+    info->entry_point = idx->ep_file;
+    info->device_bytes = idx->device_bytes;
+  });
+}
+
+int hb_index_graph_dims(const hb_index* h, uint32_t graph, uint64_t* n_nodes, uint64_t* n_edges) {
+  return guarded([&] {
+    Index* idx = as_index(h);
+    HB_REQUIRE(graph < idx->g_nodes.size(), HB_ERR_INVALID, "graph index out of range");
+    if (n_nodes) *n_nodes = idx->g_nodes[graph];
+    if (n_edges) *n_edges = idx->g_edges[graph];
+  });
+}
+
+int hb_index_graph_export(const hb_index* h, uint32_t graph, uint64_t* sketches, uint64_t* down, uint64_t* off, uint64_t* ids) {
+  return guarded([&] {
+    Index* idx = as_index(h);
+    HB_REQUIRE(idx->has_host, HB_ERR_INVALID, "index was created without keep_host");
+    HB_REQUIRE(graph < idx->host.size(), HB_ERR_INVALID, "graph index out of range");
+    const HostGraph& g = idx->host[graph];
+    if (sketches) std::memcpy(sketches, g.sk.data(), g.sk.size() * 8);
+    if (down) for (size_t i = 0; i < g.down.size(); ++i) down[i] = g.down[i];
+    if (off) std::memcpy(off, g.off.data(), g.off.size() * 8);
+    if (ids) for (size_t i = 0; i < g.ids.size(); ++i) ids[i] = g.ids[i];
+  });
+}
+
+int hb_knns_device(const hb_index* h, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, void* d_keys,
+                   void* d_dists, void* d_found, void* d_counters, void* stream) {
+  return guarded([&] {
+    Index* idx = as_index(h);
+    HB_REQUIRE(nq == 0 || (d_queries && d_keys && d_dists && d_found), HB_ERR_INVALID, "null device buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (idx->algo == HB_ALGO_BRUTEFORCE) {
+      // Indexes::Bruteforce: exact top-k; `ef` is ignored (bruteforce.rs:38).  Sorted (distance, key) order.
+      HB_REQUIRE(k >= 1, HB_ERR_INVALID, "k out of range");
+      HB_CUDA(cudaSetDevice(idx->device));
+      if (nq == 0) return;
+      uint64_t* packed = nullptr;
+      HB_CUDA(cudaMallocAsync(&packed, nq * k * 8, s));
+      try {
+        ground_truth_device(idx->d_sk, idx->n_base, 0, d_queries, nq, k, packed, s);
+        unpack_device(packed, nq * k, d_keys, d_dists, s);
+      } catch (...) {
+        cudaFreeAsync(packed, s);
+        throw;
+      }
+      cudaFreeAsync(packed, s);
+      const uint32_t nres = (uint32_t)std::min<uint64_t>(k, idx->n_base);
+      std::vector<uint32_t> f(nq, nres);
+      HB_CUDA(cudaMemcpyAsync(d_found, f.data(), nq * 4, cudaMemcpyHostToDevice, s));
+      if (d_counters) HB_CUDA(cudaMemsetAsync(d_counters, 0, nq * 16, s));
+      HB_CUDA(cudaStreamSynchronize(s));
+      return;
+    }
+    knns_device(*idx, d_queries, nq, k, ef, flags, d_keys, d_dists, d_found, d_counters, s);
+  });
+}
+
+int hb_knns(const hb_index* h, const uint64_t* queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, uint64_t* keys,
+            uint64_t* dists, uint32_t* found, hb_counters* counters) {
+  return guarded([&] {
+    Index* idx = as_index(h);
+    HB_REQUIRE(nq == 0 || (queries && keys && dists), HB_ERR_INVALID, "null host buffer");
+    HB_REQUIRE(k >= 1 && k <= HB_MAX_K, HB_ERR_INVALID, "k out of range");
+    if (nq == 0) return;
+    HB_CUDA(cudaSetDevice(idx->device));
+    DevMem<uint64_t> dq(nq * 16), dk(nq * k), dd(nq * k);
+    DevMem<uint32_t> df(nq);
+    DevMem<hb_counters> dc(counters ? nq : 0);
+    HB_CUDA(cudaMemcpy(dq.p, queries, nq * 128, cudaMemcpyHostToDevice));
+    int rc = hb_knns_device(h, dq.p, nq, k, ef, flags, dk.p, dd.p, df.p, counters ? (void*)dc.p : nullptr, nullptr);
+    if (rc != HB_OK) throw Error(rc, g_last_error);
+    HB_CUDA(cudaMemcpy(keys, dk.p, nq * k * 8, cudaMemcpyDeviceToHost));
+    HB_CUDA(cudaMemcpy(dists, dd.p, nq * k * 8, cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> f(nq);
+    HB_CUDA(cudaMemcpy(f.data(), df.p, nq * 4, cudaMemcpyDeviceToHost));
+    if (found) std::memcpy(found, f.data(), nq * 4);
+    if (counters) HB_CUDA(cudaMemcpy(counters, dc.p, nq * sizeof(hb_counters), cudaMemcpyDeviceToHost));
+    if (idx->algo == HB_ALGO_BRUTEFORCE) {
+      // rows past found are UINT64_MAX from the packed form: zero them / pad like the graph path
+      for (uint64_t i = 0; i < nq; ++i)
+        for (uint32_t j = f[i]; j < k; ++j) {
+          const bool pad = (flags & HB_PAD_LIKE_CLI) && f[i] > 0;
+          keys[i * k + j] = pad ? keys[i * k] : 0;
+          dists[i * k + j] = pad ? dists[i * k] : 0;
+        }
+    }
+    if (flags & HB_PAD_LIKE_CLI)
+      for (uint64_t i = 0; i < nq; ++i)
+        HB_REQUIRE(f[i] > 0, HB_ERR_EMPTY_RESULT, "search returned no elements (the reference panics here, main.rs:472)");
+  });
+}
+
+int hb_search(const hb_index* h, const uint64_t* query, uint32_t k, uint32_t ef, uint32_t flags, uint64_t* keys, uint64_t* dists,
+              uint32_t* found) {
+  return hb_knns(h, query, 1, k, ef, flags, keys, dists, found, nullptr);
+}
+
+int hb_ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
+                           void* d_packed, void* stream) {
+  return guarded([&] {
+    HB_REQUIRE(nq == 0 || (d_queries && d_packed), HB_ERR_INVALID, "null device buffer");
+    HB_REQUIRE(n == 0 || d_data, HB_ERR_INVALID, "null device buffer");
+    ground_truth_device(d_data, n, key_offset, d_queries, nq, k, d_packed, static_cast<cudaStream_t>(stream));
+  });
+}
+
+int hb_topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_packed_out, void* stream) {
+  return guarded([&] {
+    HB_REQUIRE(nq == 0 || (d_lists && d_packed_out), HB_ERR_INVALID, "null device buffer");
+    topk_merge_device(d_lists, n_lists, nq, k, d_packed_out, static_cast<cudaStream_t>(stream));
+  });
+}
+
+int hb_unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists, void* stream) {
+  return guarded([&] {
+    HB_REQUIRE(n == 0 || (d_packed && d_keys && d_dists), HB_ERR_INVALID, "null device buffer");
+    unpack_device(d_packed, n, d_keys, d_dists, static_cast<cudaStream_t>(stream));
+  });
+}
+
+int hb_ground_truth(const uint64_t* data, uint64_t n, const uint64_t* queries, uint64_t nq, uint32_t k, int device, uint64_t* keys,
+                    uint64_t* dists) {
+  return guarded([&] {
+    HB_REQUIRE(nq == 0 || (queries && keys && dists), HB_ERR_INVALID, "null host buffer");
+    HB_REQUIRE(n == 0 || data, HB_ERR_INVALID, "null host buffer");
+    ensure_device(device);
+    if (nq == 0) return;
+    DevMem<uint64_t> dd(n * 16), dq(nq * 16), dp(nq * k), dk(nq * k), ds(nq * k);
+    if (n) HB_CUDA(cudaMemcpy(dd.p, data, n * 128, cudaMemcpyHostToDevice));
+    HB_CUDA(cudaMemcpy(dq.p, queries, nq * 128, cudaMemcpyHostToDevice));
+    ground_truth_device(dd.p, n, 0, dq.p, nq, k, dp.p, nullptr);
+    unpack_device(dp.p, nq * k, dk.p, ds.p, nullptr);
+    HB_CUDA(cudaMemcpy(keys, dk.p, nq * k * 8, cudaMemcpyDeviceToHost));
+    HB_CUDA(cudaMemcpy(dists, ds.p, nq * k * 8, cudaMemcpyDeviceToHost));
+  });
+}
+
+int hb_synth_device(const hb_synth_params* p, uint64_t start_row, uint64_t n_rows, void* d_out, void* stream) {
+  return guarded([&] {
+    HB_REQUIRE(p && (n_rows == 0 || d_out), HB_ERR_INVALID, "null argument");
+    synth_device(*p, start_row, n_rows, d_out, static_cast<cudaStream_t>(stream));
+  });
+}
+
+int hb_build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params* p, int device, int keep_host, hb_index** out) {
+  return guarded([&] {
+    HB_REQUIRE(out && p && (n == 0 || data), HB_ERR_INVALID, "null argument");
+    *out = nullptr;
+    *out = reinterpret_cast<hb_index*>(build_hnsw(data, n, *p, device, keep_host != 0));
+  });
+}
+
+}  // extern "C"

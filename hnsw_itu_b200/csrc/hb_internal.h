@@ -1,0 +1,117 @@
+// hb_internal.h -- shared declarations of libhnswb200 (product code; never includes oracle/).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/hnsw_b200.h"
+
+namespace hb {
+
+struct Error : std::runtime_error {
+  int code;
+  Error(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+void set_last_error(const std::string& m);
+
+#define HB_CUDA(expr)                                                                                     \
+  do {                                                                                                    \
+    cudaError_t e_ = (expr);                                                                              \
+    if (e_ != cudaSuccess) {                                                                              \
+      int c_ = (e_ == cudaErrorMemoryAllocation) ? HB_ERR_OOM                                             \
+               : (e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver || e_ == cudaErrorInvalidDevice) ? HB_ERR_NO_DEVICE \
+                                                                                                        : HB_ERR_CUDA; \
+      throw hb::Error(c_, std::string(#expr) + ": " + cudaGetErrorString(e_));                            \
+    }                                                                                                     \
+  } while (0)
+
+#define HB_REQUIRE(cond, code, msg) \
+  do {                              \
+    if (!(cond)) throw hb::Error((code), (msg)); \
+  } while (0)
+
+// ---- host-side graph arrays (one per graph; graph 0 = base) -----------------
+struct HostGraph {
+  uint64_t n = 0;
+  std::vector<uint64_t> sk;    // n*16
+  std::vector<uint64_t> down;  // n (upper layers only): index into the graph below
+  std::vector<uint64_t> off;   // n+1
+  std::vector<uint32_t> ids;   // canonical (file) order
+};
+
+// ResultAttrs, cli/src/main.rs:311-320
+struct Attrs {
+  bool format_size = true;
+  std::string data = "hamming";
+  uint64_t size = 0;
+  uint32_t algo = 0;
+  double buildtime = 0.0, querytime = 0.0;
+  std::string params;
+};
+
+// per-device scratch of the search kernel, cached on the index
+struct SearchWorkspace {
+  uint32_t vcap_log2 = 0;  // visited-table capacity per warp slot (log2, 32-bit words)
+  uint32_t slots = 0;      // resident warp slots the tables were sized for
+  uint32_t spill_cap = 0;
+  uint32_t* vis = nullptr;     // slots << vcap_log2 words, all EMPTY between launches
+  uint32_t* spill = nullptr;   // slots * spill_cap
+  uint32_t* ctl = nullptr;     // [0] query counter, [1] overflow flag
+  uint32_t* qstatus = nullptr; // per query (capacity qcap)
+  uint32_t* qmap = nullptr;    // retry indirection (capacity qcap)
+  uint64_t qcap = 0;
+};
+
+struct Index {
+  int device = 0;
+  int algo = HB_ALGO_HNSW;
+  Attrs attrs;
+  bool has_host = false;
+  std::vector<HostGraph> host;  // kept when keep_host
+  // dims (always kept)
+  std::vector<uint64_t> g_nodes, g_edges, g_base;  // g_base[g] = first global id of graph g
+  int64_t ep_file = -1;
+  // device arrays: one id space over all graphs (base first)
+  uint64_t n_total = 0, n_base = 0;
+  uint32_t stride = 0;        // words per adjacency row, multiple of 32 (row = one or more 128-B lines)
+  uint4* d_sk = nullptr;      // n_total rows of 128 B
+  uint32_t* d_adj = nullptr;  // n_total * stride; word 0 = degree, then global neighbour ids
+  uint32_t* d_down = nullptr; // n_total - n_base: global id of the same point one graph below
+  uint32_t ep_gid = 0;
+  uint64_t device_bytes = 0;
+  int sm_count = 0;
+  mutable std::mutex mu;  // serialises launches that share the workspace
+  mutable SearchWorkspace ws;
+  ~Index();
+};
+
+// idx_format.cpp
+void read_idx_file(const char* path, Attrs& attrs, int& algo, std::vector<HostGraph>& graphs, int64_t& ep);
+void write_idx_file(const char* path, const Attrs& attrs, int algo, const std::vector<HostGraph>& graphs, int64_t ep);
+
+// index.cu
+Index* index_from_host(int algo, std::vector<HostGraph>&& graphs, int64_t ep, int device, bool keep_host);
+void ensure_device(int device);
+
+// search.cu
+void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, void* d_keys,
+                 void* d_dists, void* d_found, void* d_counters, cudaStream_t stream);
+
+// bruteforce.cu
+void ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
+                         void* d_packed, cudaStream_t stream);
+void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream);
+void unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists, cudaStream_t stream);
+
+// synth.cu
+void synth_device(const hb_synth_params& p, uint64_t start, uint64_t n, void* d_out, cudaStream_t stream);
+
+// builder.cu
+Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& p, int device, bool keep_host);
+
+}  // namespace hb

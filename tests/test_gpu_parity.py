@@ -1,0 +1,208 @@
+"""GPU parity: the CUDA path through the C ABI vs the CPU oracle on the same inputs.
+Bit-exact bar (integer work): identical ids, distances, found counts and work counters."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+CASES = [(10, 64), (10, 16), (1, 1), (10, 4), (25, 40), (100, 100)]
+
+
+@pytest.fixture(scope="module")
+def hb():
+    import hnsw_itu_b200 as m
+    return m
+
+
+def _queries():
+    return np.fromfile(os.path.join(G, "tiny_queries.u64"), dtype=np.uint64).reshape(-1, 16)
+
+
+def _to_gpu(hb, oidx, keep_host=True):
+    return hb.index_from_parts(oidx.algo, oidx.graphs(), oidx.ep, keep_host=keep_host)
+
+
+def _assert_same(hidx, oidx, q, k, ef, pad=False):
+    ok, od, of, oc = oidx.knns(q, k, ef, pad=pad, counters=True)
+    gk, gd, gf, gc = hidx.knns_arrays(q, k, ef, pad=pad, counters=True)
+    assert np.array_equal(gf, of), (k, ef)
+    assert np.array_equal(gk, ok), (k, ef)
+    assert np.array_equal(gd, od), (k, ef)
+    assert np.array_equal(gc.astype(np.uint64), oc), (k, ef)
+
+
+def test_golden_fixtures_from_idx_file(hb):
+    """read_index of the committed .idx bytes, then the committed expected ids/distances."""
+    exp = np.load(os.path.join(G, "tiny_expected.npz"))
+    q = _queries()
+    for name in ("hnsw", "nsw"):
+        idx = hb.read_index(os.path.join(G, f"tiny_{name}.idx"))
+        assert idx.algo == name
+        for k, ef in CASES:
+            keys, dists, found = idx.knns_arrays(q, k, ef)
+            assert np.array_equal(keys, exp[f"{name}_k{k}_ef{ef}_keys"]), (name, k, ef)
+            assert np.array_equal(dists, exp[f"{name}_k{k}_ef{ef}_dists"]), (name, k, ef)
+            assert np.array_equal(found, exp[f"{name}_k{k}_ef{ef}_found"]), (name, k, ef)
+        if name == "hnsw":
+            _, _, _, ctr = idx.knns_arrays(q, 10, 64, counters=True)
+            assert np.array_equal(ctr.astype(np.uint64), exp["hnsw_k10_ef64_ctr"])
+    bf = hb.read_index(os.path.join(G, "tiny_bruteforce.idx"))
+    assert bf.algo == "bruteforce" and bf.size() == 100
+
+
+def test_idx_write_roundtrip(hb, oracle, tmp_path):
+    import filecmp
+    for name in ("hnsw", "nsw", "bruteforce"):
+        src = os.path.join(G, f"tiny_{name}.idx")
+        dst = str(tmp_path / f"{name}.idx")
+        hb.read_index(src).write_index(dst)
+        assert filecmp.cmp(src, dst, shallow=False)
+
+
+@pytest.mark.parametrize("distinct_planes", [1024, 64, 16])
+def test_search_parity_vs_oracle(hb, oracle, distinct_planes):
+    from oracle import oracle as orc
+    p = orc.SynthParams(latent_dim=16, n_clusters=64, centre_scale=1, noise_scale=1, distinct_planes=distinct_planes)
+    data = oracle.synth(6000, 31, p)
+    q = oracle.synth(300, 32, p)
+    oidx = oracle.build(data, "hnsw", efc=32, m=8, M=24, parallel=False, rayon_threads=4)
+    hidx = _to_gpu(hb, oidx)
+    assert hidx.size() == 6000
+    for ef in (0, 1, 2, 10, 16, 33, 64, 96, 256):
+        for k in (1, 10, 64, 100):
+            _assert_same(hidx, oidx, q, k, ef)
+    _assert_same(hidx, oidx, q, 10, 4, pad=True)
+
+
+def test_search_parity_reference_parameters(hb, oracle):
+    """m=24 M=256 c=96 (the reference's CLI defaults) incl. hub rows longer than one 128-B line."""
+    data = oracle.synth(20000, 41)
+    q = oracle.synth(500, 42)
+    oidx = oracle.build(data, "hnsw", efc=96, m=24, M=256, parallel=False)
+    hidx = _to_gpu(hb, oidx, keep_host=False)
+    for ef in (16, 64, 96, 128):
+        _assert_same(hidx, oidx, q, 10, ef)
+    # Index::search == knns of one
+    res = hidx.search(q[0], 10, 64)
+    exp = oidx.search(q[0], 10, 64)
+    assert [(d.distance, d.key) for d in res] == exp
+    assert res == sorted(res)
+
+
+def test_nsw_and_edge_cases(hb, oracle):
+    from oracle import oracle as orc
+    p = orc.SynthParams(latent_dim=8, n_clusters=16, distinct_planes=32)
+    data = oracle.synth(1500, 21, p)
+    q = oracle.synth(64, 22, p)
+    onsw = oracle.build(data, "nsw", efc=16, m=4, M=8, parallel=False)
+    hnsw = _to_gpu(hb, onsw)
+    for ef in (1, 5, 40):
+        _assert_same(hnsw, onsw, q, 10, ef)
+    # single node (self loop), fewer nodes than k, padding like the CLI
+    one = oracle.build(data[:1], "hnsw", efc=8, m=4, M=8, parallel=False)
+    h1 = _to_gpu(hb, one)
+    _assert_same(h1, one, q[:3], 10, 64)
+    _assert_same(h1, one, q[:3], 10, 64, pad=True)
+    # empty index: HNSW::search returns [] (hnsw.rs:282); padding then fails like the reference's panic
+    empty = hb.index_from_parts("hnsw", [{"sketches": np.zeros((0, 16), dtype=np.uint64), "off": np.zeros(1, dtype=np.uint64),
+                                          "ids": np.zeros(0, dtype=np.uint64)}], None)
+    keys, dists, found = empty.knns_arrays(q[:2], 5, 10)
+    assert (found == 0).all() and (keys == 0).all()
+    with pytest.raises(hb.HbError) as e:
+        empty.knns_arrays(q[:2], 5, 10, pad=True)
+    assert e.value.code == 7
+    # zero queries
+    k0, d0, f0 = hnsw.knns_arrays(np.zeros((0, 16), dtype=np.uint64), 5, 10)
+    assert k0.shape == (0, 5)
+
+
+def test_visited_table_overflow_retry(hb, oracle):
+    """ef far above what the first visited-table size allows for: forces the exact-overflow retry path."""
+    from oracle import oracle as orc
+    p = orc.SynthParams(latent_dim=8, n_clusters=4, distinct_planes=1024)
+    data = oracle.synth(30000, 51, p)
+    q = oracle.synth(40, 52, p)
+    oidx = oracle.build(data, "hnsw", efc=32, m=16, M=256, parallel=False)
+    hidx = _to_gpu(hb, oidx, keep_host=False)
+    _assert_same(hidx, oidx, q, 10, 16)   # table starts at 4096 slots; hub-heavy graph overflows it for some queries
+    _assert_same(hidx, oidx, q, 100, 1000)
+
+
+def test_ground_truth_parity(hb, oracle):
+    from oracle import oracle as orc
+    for dp, n, nq, k in ((1024, 5000, 70, 10), (32, 3000, 33, 100), (1024, 7, 5, 10), (1024, 1, 3, 1)):
+        p = orc.SynthParams(latent_dim=8, n_clusters=16, distinct_planes=dp)
+        data = oracle.synth(n, 61, p)
+        q = oracle.synth(nq, 62, p)
+        gk, gd = hb.ground_truth(data, q, k)
+        ok, od = oracle.ground_truth(data, q, k)
+        m = min(n, k)
+        assert np.array_equal(gk[:, :m], ok[:, :m]) and np.array_equal(gd[:, :m], od[:, :m]), (dp, n, nq, k)
+        if n < k:
+            assert (gk[:, m:] == np.uint64(2**64 - 1)).all()
+    exp = np.load(os.path.join(G, "tiny_expected.npz"))
+    data = oracle.load_idx(os.path.join(G, "tiny_hnsw.idx")).graph(0)["sketches"]
+    gk, gd = hb.ground_truth(data, _queries(), 10)
+    assert np.array_equal(gk, exp["gt_k10_keys"]) and np.array_equal(gd, exp["gt_k10_dists"])
+    # Indexes::Bruteforce through Index::knns (sorted order; ef ignored)
+    bf = hb.read_index(os.path.join(G, "tiny_bruteforce.idx"))
+    bk, bd, bfnd = bf.knns_arrays(_queries(), 10, 3)
+    ok, od = oracle.ground_truth(data[:100], _queries(), 10)
+    assert np.array_equal(bk, ok) and np.array_equal(bd, od) and (bfnd == 10).all()
+
+
+def test_sharded_ground_truth_merge(hb, oracle):
+    """config 4's shape on one GPU: per-shard top-k with key offsets, then the exact (distance,key) merge."""
+    import torch
+    from hnsw_itu_b200 import _lib
+    data = oracle.synth(4000, 71)
+    q = oracle.synth(50, 72)
+    k, shards = 10, 4
+    dq = torch.from_numpy(q.view(np.int64)).cuda()
+    lists = torch.empty((shards, len(q), k), dtype=torch.int64, device="cuda")
+    for s in range(shards):
+        part = torch.from_numpy(data[s * 1000:(s + 1) * 1000].view(np.int64)).cuda()
+        _lib.check(_lib.lib().hb_ground_truth_device(part.data_ptr(), 1000, s * 1000, dq.data_ptr(), len(q), k, lists[s].data_ptr(), None))
+    merged = torch.empty((len(q), k), dtype=torch.int64, device="cuda")
+    _lib.check(_lib.lib().hb_topk_merge_device(lists.data_ptr(), shards, len(q), k, merged.data_ptr(), None))
+    keys = torch.empty_like(merged); dists = torch.empty_like(merged)
+    _lib.check(_lib.lib().hb_unpack_device(merged.data_ptr(), merged.numel(), keys.data_ptr(), dists.data_ptr(), None))
+    torch.cuda.synchronize()
+    ok, od = oracle.ground_truth(data, q, k)
+    assert np.array_equal(keys.cpu().numpy().view(np.uint64), ok)
+    assert np.array_equal(dists.cpu().numpy().view(np.uint64), od)
+
+
+def test_synth_kernel_matches_oracle(hb, oracle):
+    import torch
+    from oracle import oracle as orc
+    for p in (orc.SynthParams(), orc.SynthParams(latent_dim=12, n_clusters=24, distinct_planes=128)):
+        n, start = 1000, 12345
+        out = torch.empty((n, 16), dtype=torch.int64, device="cuda")
+        hb.synth_sketches(out.data_ptr(), n, 1003, start=start, latent_dim=p.latent_dim, n_clusters=p.n_clusters,
+                          centre_scale=p.centre_scale, noise_scale=p.noise_scale, distinct_planes=p.distinct_planes)
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy().view(np.uint64), oracle.synth(n, 1003, p, start=start))
+
+
+def test_size_independent_properties(hb, oracle):
+    """Properties that hold at any size: ascending (distance,key), no duplicate keys, distances recomputable,
+    self-query finds itself at distance 0, ground truth of a permuted shard union is unchanged."""
+    data = oracle.synth(50000, 81)
+    oidx = oracle.build(data[:20000], "hnsw", efc=48, m=12, M=64, parallel=False)
+    hidx = _to_gpu(hb, oidx, keep_host=False)
+    q = data[:256]
+    keys, dists, found = hidx.knns_arrays(q, 10, 64)
+    assert (found == 10).all()
+    assert (keys[:, 0] == np.arange(256)).all() and (dists[:, 0] == 0).all()
+    packed = (dists.astype(np.uint64) << np.uint64(32)) | keys
+    assert (np.diff(packed.astype(np.int64), axis=1) > 0).all()
+    for i in range(0, 256, 37):
+        for j in range(10):
+            assert oracle.hamming(q[i], data[int(keys[i, j])]) == int(dists[i, j])
+    gk, gd = hb.ground_truth(data, q[:32], 10)
+    assert (gk[:, 0] == np.arange(32)).all() and (gd[:, 0] == 0).all()
+    assert (np.diff(((gd << np.uint64(32)) | gk).astype(np.int64), axis=1) > 0).all()
