@@ -41,6 +41,21 @@ constexpr uint32_t kFull = 0xFFFFFFFFu;
 constexpr uint32_t kEmpty = 0xFFFFFFFFu;
 constexpr int kWarpsPerBlock = 4;
 
+#ifdef HB_DEBUG_BOUNDS
+#define HB_CHK(cond, code, val)                                   \
+  do {                                                            \
+    if (!(cond)) {                                                \
+      if (atomicCAS(p.ctl + 2, 0u, (uint32_t)(code)) == 0u) {     \
+        p.ctl[3] = (uint32_t)(val);                               \
+        p.ctl[4] = q;                                             \
+      }                                                           \
+      return;                                                     \
+    }                                                             \
+  } while (0)
+#else
+#define HB_CHK(cond, code, val) do {} while (0)
+#endif
+
 struct SearchParams {
   const uint4* sk;
   const uint32_t* adj;
@@ -56,6 +71,7 @@ struct SearchParams {
   uint32_t* ctl;      // [0] next query, [1] overflow flag
   uint32_t* qstatus;  // per query: 0 ok, 1 visited table full, 2 tie stack full
   uint32_t stride;
+  uint32_t n_total;
   uint32_t n_base;
   uint32_t n_upper;  // number of upper graphs (0 for NSW)
   uint32_t ep_gid;
@@ -107,6 +123,7 @@ __device__ __forceinline__ void beam_insert(uint64_t* w, uint32_t ef, Beam& b, u
   const bool full = b.size >= ef;
   uint64_t ev = 0;
   if (full) ev = w[ef - 1];  // the element pop_max() removes (never the one being pushed: d < F)
+  __syncwarp();              // every lane has read ev before lane 0 may overwrite w[ef - 1] (pos == ef - 1: no shift below)
   const int hi = full ? (int)ef - 2 : (int)b.size - 1;
   if (hi >= (int)pos) {
     for (int base = hi & ~31; base + 31 >= (int)pos; base -= 32) {
@@ -165,6 +182,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) hnsw_search_kernel(con
       const uint32_t ef = (g == 0) ? p.ef : 1u;  // hnsw.rs:286 (ef = 1 above the base)
       // ---- nsw::search(graph g, q, ef, cur) ---------------------------------
       {
+        HB_CHK(cur < p.n_total, 1, cur);
         uint32_t d0 = popc4(__ldg(p.sk + (size_t)cur * 8 + sub), qv);  // nsw.rs:140-141
         d0 += __shfl_xor_sync(kFull, d0, 1);
         d0 += __shfl_xor_sync(kFull, d0, 2);
@@ -206,15 +224,21 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) hnsw_search_kernel(con
         }
         ++X;
         // ---- for e in graph.neighborhood(c.key)  (nsw.rs:156) ------------------
+        HB_CHK(ckey < p.n_total, 2, ckey);
         const uint32_t* row = p.adj + (size_t)ckey * p.stride;
         uint32_t word = __ldg(row + lane);
         const uint32_t deg = __shfl_sync(kFull, word, 0);
+#ifdef HB_DEBUG_BOUNDS
+        if (deg >= p.stride) { p.ctl[5] = ckey; p.ctl[6] = X; p.ctl[7] = (uint32_t)g | (ci < 0 ? 0x100u : 0u) | (b.size << 16); }
+#endif
+        HB_CHK(deg < p.stride, 3, deg);
         E += deg;
         if (vcount + deg > vlimit) { status = 1; break; }
         for (uint32_t base = 0; base <= deg; base += 32) {
           const uint32_t wi = base + lane;
           if (base) word = (wi <= deg) ? __ldg(row + wi) : 0u;
           const bool valid = (wi >= 1u) && (wi <= deg);
+          HB_CHK(__all_sync(kFull, !valid || word < p.n_total), 4, word);
           const bool isnew = valid && visit(vis, vmask, vshift, word);  // nsw.rs:157-161
           const uint32_t nm = __ballot_sync(kFull, isnew);
           if (!nm) continue;
@@ -263,6 +287,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) hnsw_search_kernel(con
         }
         if (status) break;
       }
+      HB_CHK(!(g > 0 && status == 0) || (pk_key(w[0]) >= p.n_base && pk_key(w[0]) < p.n_total), 5, pk_key(w[0]));
       if (g > 0 && status == 0) cur = __ldg(p.down + (pk_key(w[0]) - p.n_base));  // hnsw.rs:288-292 (.point.1)
       __syncwarp();
     }
@@ -313,7 +338,7 @@ void ensure_workspace(const Index& idx, uint32_t vcap_log2, uint32_t slots, uint
     ws.vcap_log2 = vcap_log2;
     ws.slots = slots;
   }
-  if (!ws.ctl) HB_CUDA(cudaMalloc(&ws.ctl, 2 * sizeof(uint32_t)));
+  if (!ws.ctl) HB_CUDA(cudaMalloc(&ws.ctl, 8 * sizeof(uint32_t)));
   if (ws.qcap < nq) {
     cudaFree(ws.qstatus);
     cudaFree(ws.qmap);
@@ -358,6 +383,7 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   p.counters = static_cast<uint4*>(d_counters);
   p.stride = idx.stride;
   p.n_base = (uint32_t)idx.n_base;
+  p.n_total = (uint32_t)idx.n_total;
   p.n_upper = (uint32_t)idx.g_nodes.size() - 1;
   p.ep_gid = idx.ep_gid;
   p.ef = ef;
@@ -394,12 +420,17 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     p.nq = (uint32_t)todo;
     p.vcap_log2 = ws.vcap_log2;
     p.spill_cap = ws.spill_cap;
-    HB_CUDA(cudaMemsetAsync(ws.ctl, 0, 2 * sizeof(uint32_t), stream));
+    HB_CUDA(cudaMemsetAsync(ws.ctl, 0, 8 * sizeof(uint32_t), stream));
     hnsw_search_kernel<<<blocks, kWarpsPerBlock * 32, smem, stream>>>(p);
     HB_CUDA(cudaGetLastError());
-    uint32_t h_ctl[2] = {0, 0};
+    uint32_t h_ctl[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     HB_CUDA(cudaMemcpyAsync(h_ctl, ws.ctl, sizeof h_ctl, cudaMemcpyDeviceToHost, stream));
     HB_CUDA(cudaStreamSynchronize(stream));
+#ifdef HB_DEBUG_BOUNDS
+    HB_REQUIRE(h_ctl[2] == 0, HB_ERR_INTERNAL,
+               "bounds check " + std::to_string(h_ctl[2]) + " value " + std::to_string(h_ctl[3]) + " query " + std::to_string(h_ctl[4]) +
+                   " vcap_log2 " + std::to_string(vcap_log2) + " retry " + std::to_string((int)retry) + " ckey " + std::to_string(h_ctl[5]) + " X " + std::to_string(h_ctl[6]) + " g/sp/size " + std::to_string(h_ctl[7]));
+#endif
     if (!h_ctl[1]) break;
     // some queries outgrew their visited table / tie stack: rerun exactly those with 4x the capacity
     HB_REQUIRE(vcap_log2 < vcap_max_log2, HB_ERR_INTERNAL, "visited table overflow at maximum capacity");

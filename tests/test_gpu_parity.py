@@ -92,6 +92,17 @@ def test_search_parity_reference_parameters(hb, oracle):
     assert res == sorted(res)
 
 
+def test_insert_at_last_beam_slot_regression(hb, oracle):
+    """Inputs that once exposed a missing warp barrier in beam_insert (insert at position ef-1 of a full beam):
+    some lanes then saw the new element as the evicted one and the warp's state diverged."""
+    data = oracle.synth(20000, 1003)
+    q = oracle.synth(2000, 1004)
+    oidx = oracle.build(data, "hnsw", efc=96, m=24, M=256, parallel=False)
+    hidx = _to_gpu(hb, oidx, keep_host=False)
+    for ef in (16, 64):
+        _assert_same(hidx, oidx, q, 10, ef)
+
+
 def test_nsw_and_edge_cases(hb, oracle):
     from oracle import oracle as orc
     p = orc.SynthParams(latent_dim=8, n_clusters=16, distinct_planes=32)
