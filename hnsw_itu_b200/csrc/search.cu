@@ -30,8 +30,10 @@
 //     distance equals the current worst distance F (break is strict, nsw.rs:152);
 //     such elements are evicted in decreasing (distance, key) order, so a STACK of
 //     keys sharing one distance reproduces pop_min over them; it dies when F drops.
+#include <cstdlib>
 #include <memory>
 
+#include "beam.cuh"
 #include "hb_internal.h"
 
 namespace hb {
@@ -316,11 +318,88 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) hnsw_search_kernel(con
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fast path (ef <= 256): beam in registers, recently-seen cache in shared memory (beam.cuh).
+// Queries whose boundary-tie stack overflows are flagged and rerun on the large-capacity kernel above.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kFastSpillCap = 64;
+
+template <int R>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) hnsw_search_fast_kernel(const SearchParams p, uint32_t cache_log2) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const size_t per_warp = ((size_t)4 << cache_log2) + 32 * 4 + kFastSpillCap * 4;
+  unsigned char* mine = smem_raw + wib * per_warp;
+  WarpScratch ws;
+  ws.cache = reinterpret_cast<uint32_t*>(mine);
+  ws.cache_shift = 32u - cache_log2;
+  ws.ids = reinterpret_cast<uint32_t*>(mine + ((size_t)4 << cache_log2));
+  uint32_t* const spill = ws.ids + 32;
+  const GraphView gv{p.sk, p.adj, p.stride};
+  const uint32_t sub = lane & 7u;
+
+  for (;;) {
+    uint32_t qi = 0;
+    if (lane == 0) qi = atomicAdd(p.ctl, 1u);
+    qi = __shfl_sync(kFullMask, qi, 0);
+    if (qi >= p.nq) break;
+    const uint32_t q = p.qmap ? p.qmap[qi] : qi;
+    const uint4 qv = __ldg(p.queries + (size_t)q * 8 + sub);
+    cache_clear(ws);
+
+    SearchCounters c;
+    uint32_t status = 0;
+    uint32_t cur = p.ep_gid;
+    BeamRegs<R> b;
+    for (int g = (int)p.n_upper; g >= 0 && status == 0; --g) {
+      const uint32_t ef = (g == 0) ? p.ef : 1u;  // hnsw.rs:286 (ef = 1 above the base)
+      beam_search<R>(gv, qv, ef, cur, ws, spill, kFastSpillCap, b, c, status);
+      if (g > 0 && status == 0) cur = __ldg(p.down + (bm_key(b.at(0)) - p.n_base));  // hnsw.rs:288-292 (.point.1)
+    }
+
+    // ---- drain_asc().take(k) (+ Indexes::search padding) ----
+    const uint32_t nres = status ? 0u : min(b.size, p.k);
+    const uint64_t first = b.at(0);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint32_t j = lane * R + r;
+      if (j < nres) {
+        p.keys[(size_t)q * p.k + j] = bm_key(b.w[r]);
+        p.dists[(size_t)q * p.k + j] = bm_dist(b.w[r]);
+      }
+    }
+    for (uint32_t j = nres + lane; j < p.k; j += 32) {
+      const bool pad = (p.flags & HB_PAD_LIKE_CLI) && nres;
+      p.keys[(size_t)q * p.k + j] = pad ? bm_key(first) : 0;
+      p.dists[(size_t)q * p.k + j] = pad ? bm_dist(first) : 0;
+    }
+    if (lane == 0) {
+      p.found[q] = nres;
+      p.qstatus[q] = status;
+      if (status) atomicOr(p.ctl + 1, 1u);
+      if (p.counters) p.counters[q] = make_uint4(c.X, c.E, c.V, c.A);
+    }
+    __syncwarp();
+  }
+}
+
+struct FastLaunch {
+  void (*kernel)(const SearchParams, uint32_t);
+};
+FastLaunch fast_kernel_for(uint32_t ef) {
+  if (ef <= 32) return {hnsw_search_fast_kernel<1>};
+  if (ef <= 64) return {hnsw_search_fast_kernel<2>};
+  if (ef <= 128) return {hnsw_search_fast_kernel<4>};
+  return {hnsw_search_fast_kernel<8>};
+}
+
 uint32_t ceil_log2(uint64_t x) {
   uint32_t l = 0;
   while ((1ull << l) < x) ++l;
   return l;
 }
+
+void ensure_common(const Index& idx, uint64_t nq);
 
 void ensure_workspace(const Index& idx, uint32_t vcap_log2, uint32_t slots, uint64_t nq) {
   SearchWorkspace& ws = idx.ws;
@@ -338,6 +417,11 @@ void ensure_workspace(const Index& idx, uint32_t vcap_log2, uint32_t slots, uint
     ws.vcap_log2 = vcap_log2;
     ws.slots = slots;
   }
+  ensure_common(idx, nq);
+}
+
+void ensure_common(const Index& idx, uint64_t nq) {
+  SearchWorkspace& ws = idx.ws;
   if (!ws.ctl) HB_CUDA(cudaMalloc(&ws.ctl, 8 * sizeof(uint32_t)));
   if (ws.qcap < nq) {
     cudaFree(ws.qstatus);
@@ -406,6 +490,42 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   uint64_t todo = nq;
   bool retry = false;
   std::vector<uint32_t> h_status, h_map;
+
+  // ---- fast path: beam in registers (ef <= 256) ------------------------------------------------
+  static const bool force_large = std::getenv("HB_FORCE_LARGE") != nullptr;
+  if (ef <= 256 && !force_large) {
+    static const int env_cache = std::getenv("HB_CACHE_LOG2") ? std::atoi(std::getenv("HB_CACHE_LOG2")) : 0;
+    uint32_t cache_log2 = env_cache >= 5 && env_cache <= 13 ? (uint32_t)env_cache : 10u;
+    const FastLaunch fl = fast_kernel_for(ef);
+    const size_t fsmem = (size_t)kWarpsPerBlock * (((size_t)4 << cache_log2) + 32 * 4 + kFastSpillCap * 4);
+    HB_CUDA(cudaFuncSetAttribute(fl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+    int fbps = 0;
+    HB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fbps, fl.kernel, kWarpsPerBlock * 32, fsmem));
+    HB_REQUIRE(fbps >= 1, HB_ERR_INTERNAL, "fast search kernel does not fit on an SM");
+    const uint32_t fblocks = (uint32_t)std::min<uint64_t>((uint64_t)idx.sm_count * fbps, (nq + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    ensure_common(idx, nq);
+    const SearchWorkspace& ws = idx.ws;
+    p.ctl = ws.ctl;
+    p.qstatus = ws.qstatus;
+    p.qmap = nullptr;
+    p.nq = (uint32_t)nq;
+    HB_CUDA(cudaMemsetAsync(ws.ctl, 0, 8 * sizeof(uint32_t), stream));
+    fl.kernel<<<fblocks, kWarpsPerBlock * 32, fsmem, stream>>>(p, cache_log2);
+    HB_CUDA(cudaGetLastError());
+    uint32_t h_ctl[2] = {0, 0};
+    HB_CUDA(cudaMemcpyAsync(h_ctl, ws.ctl, sizeof h_ctl, cudaMemcpyDeviceToHost, stream));
+    HB_CUDA(cudaStreamSynchronize(stream));
+    if (!h_ctl[1]) return;
+    // boundary-tie stack overflow (tie-heavy data): rerun exactly those queries on the large-capacity kernel
+    h_status.resize(nq);
+    HB_CUDA(cudaMemcpy(h_status.data(), ws.qstatus, nq * 4, cudaMemcpyDeviceToHost));
+    for (uint64_t i = 0; i < nq; ++i) if (h_status[i]) h_map.push_back((uint32_t)i);
+    HB_REQUIRE(!h_map.empty(), HB_ERR_INTERNAL, "overflow flag set without an overflowed query");
+    HB_CUDA(cudaMemcpy(ws.qmap, h_map.data(), h_map.size() * 4, cudaMemcpyHostToDevice));
+    todo = h_map.size();
+    retry = true;
+  }
+
   for (;;) {
     uint32_t blocks = (uint32_t)std::min<uint64_t>(max_blocks, (todo + kWarpsPerBlock - 1) / kWarpsPerBlock);
     // bound scratch memory for the (rare) big-table retries

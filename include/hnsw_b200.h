@@ -74,7 +74,8 @@ typedef struct hb_index_info {
 typedef struct hb_counters {
   uint32_t expansions;   /* X: candidates expanded */
   uint32_t ids_scanned;  /* E: neighbour ids iterated */
-  uint32_t dist_evals;   /* V: distance evaluations == |visited| */
+  uint32_t dist_evals;   /* V: distance evaluations performed; >= |visited| of the reference (the ef <= 256 path keeps a
+                            recently-seen cache instead of an exact visited set; results, X, E and A are unaffected) */
   uint32_t accepted;     /* A: pushes into the beam */
 } hb_counters;
 

@@ -292,15 +292,33 @@ void synth_rows(const SynthParams& p, uint64_t start, uint64_t n, uint64_t* out)
 // before the CUDA kernel is trusted with it.
 // ---------------------------------------------------------------------------
 uint64_t g_spill_pops = 0;  // how often the boundary-tie stack supplied a candidate (test visibility)
+// 0: exact visited set (nsw.rs:143).  c > 0: the kernel's formulation -- a direct-mapped cache of 2^c
+// recently seen ids (a hit is certainly visited; a miss may be a revisit) plus "already in w" dedupe.
+// A revisited node that is not in w was either rejected or evicted earlier, so its distance is >= the
+// current F of a full beam and it is rejected again: results, X, E and A are unchanged, only V grows.
+int g_cache_log2 = 0;
+struct VisitCache {
+  std::vector<uint32_t> tab;
+  uint32_t shift = 0;
+  explicit VisitCache(int log2) : tab((size_t)1 << log2, 0xFFFFFFFFu), shift(32u - (uint32_t)log2) {}
+  bool test_and_set(uint32_t gid) {  // true when gid was cached (certainly visited)
+    uint32_t h = (gid * 0x9E3779B1u) >> shift;
+    if (tab[h] == gid) return true;
+    tab[h] = gid;
+    return false;
+  }
+};
 template <class G, class Q, class DF>
-std::vector<Dist> search_bounded(const G& graph, const Q& query, size_t ef, Idx ep, DF dist, Counters* ctr) {
+std::vector<Dist> search_bounded(const G& graph, const Q& query, size_t ef, Idx ep, DF dist, Counters* ctr,
+                                 VisitCache* cache = nullptr, uint64_t gid_base = 0) {
   if (ef == 0) ef = 1;
   struct El { Dist d; bool expanded; };
   std::vector<El> w;
   std::vector<uint64_t> spill;  // keys; all share distance spill_d
   uint64_t spill_d = 0;
   VisitedSet visited(2048);
-  visited.insert(ep);
+  if (!cache) visited.insert(ep);
+  else cache->test_and_set((uint32_t)(gid_base + ep));
   Counters c;
   c.V = 1;
   w.push_back(El{Dist{(uint64_t)dist(*graph.get(ep), query), ep}, false});
@@ -316,14 +334,16 @@ std::vector<Dist> search_bounded(const G& graph, const Q& query, size_t ef, Idx 
     ++c.X;
     for (Idx e : graph.neighborhood(ckey)) {
       ++c.E;
-      if (!visited.insert(e)) continue;
+      if (!cache) { if (!visited.insert(e)) continue; }
+      else if (cache->test_and_set((uint32_t)(gid_base + e))) continue;
       ++c.V;
       Dist ed{(uint64_t)dist(*graph.get(e), query), e};
       F = w.back().d.distance;
       if (ed.distance >= F && w.size() >= ef) continue;
-      ++c.A;
       size_t pos = 0;
       while (pos < w.size() && w[pos].d < ed) ++pos;
+      if (cache && pos < w.size() && w[pos].d.key == e) continue;  // revisit of a node that is still in w
+      ++c.A;
       bool full = w.size() >= ef;
       El ev{};
       if (full) { ev = w.back(); w.pop_back(); }
@@ -341,16 +361,21 @@ std::vector<Dist> search_bounded(const G& graph, const Q& query, size_t ef, Idx 
   for (auto& e : w) out.push_back(e.d);
   return out;
 }
-
 std::vector<Dist> hnsw_search_bounded(const HNSWc& h, const Sketch& q, size_t k, size_t ef, Counters* ctr) {
   if (!h.ep) return {};
   Idx cur = *h.ep;
   auto ldist = [&](const std::pair<Sketch, Idx>& n, const Sketch& qq) { return SketchDistance{}(n.first, qq); };
+  std::optional<VisitCache> cache;
+  if (g_cache_log2 > 0) cache.emplace(g_cache_log2);
+  VisitCache* cp = cache ? &*cache : nullptr;
+  std::vector<uint64_t> gbase(h.layers.size() + 1, 0);  // one id space over all graphs, base first (as on the device)
+  gbase[0] = 0;
+  for (size_t l = 0; l < h.layers.size(); ++l) gbase[l + 1] = gbase[l] + (l == 0 ? h.base.size() : h.layers[l - 1].size());
   for (size_t l = h.layers.size(); l-- > 0;) {
-    auto w = search_bounded(h.layers[l], q, 1, cur, ldist, ctr);
+    auto w = search_bounded(h.layers[l], q, 1, cur, ldist, ctr, cp, gbase[l + 1]);
     cur = h.layers[l].get(w.front().key)->second;
   }
-  auto v = search_bounded(h.base, q, ef, cur, SketchDistance{}, ctr);
+  auto v = search_bounded(h.base, q, ef, cur, SketchDistance{}, ctr, cp, 0);
   if (v.size() > k) v.resize(k);
   return v;
 }
@@ -573,6 +598,7 @@ int orc_knns(const void* h, const uint64_t* queries, uint64_t nq, uint64_t k, ui
 }
 
 uint64_t orc_debug_spill_pops() { return g_spill_pops; }
+void orc_debug_set_cache_log2(int c) { g_cache_log2 = c; }
 // Same contract as orc_knns but through the bounded-beam model (HNSW / NSW only).
 int orc_knns_bounded(const void* h, const uint64_t* queries, uint64_t nq, uint64_t k, uint64_t ef, uint64_t* keys,
                      uint64_t* dists, uint32_t* found, uint64_t* counters) {
@@ -584,7 +610,12 @@ int orc_knns_bounded(const void* h, const uint64_t* queries, uint64_t nq, uint64
       std::vector<Dist> res;
       if (auto* x = std::get_if<HNSWc>(&idx.v)) res = hnsw_search_bounded(*x, q, k, ef, &c);
       else if (auto* n = std::get_if<NSWc>(&idx.v)) {
-        if (n->ep) { res = search_bounded(n->graph, q, ef, *n->ep, SketchDistance{}, &c); if (res.size() > k) res.resize(k); }
+        if (n->ep) {
+          std::optional<VisitCache> cache;
+          if (g_cache_log2 > 0) cache.emplace(g_cache_log2);
+          res = search_bounded(n->graph, q, ef, *n->ep, SketchDistance{}, &c, cache ? &*cache : nullptr, 0);
+          if (res.size() > k) res.resize(k);
+        }
       } else throw std::runtime_error("bounded model: graph indexes only");
       found[i] = (uint32_t)res.size();
       for (size_t j = 0; j < k; ++j) {
