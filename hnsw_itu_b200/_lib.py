@@ -32,7 +32,8 @@ class HbError(RuntimeError):
 class IndexInfo(C.Structure):
     _fields_ = [("algo", C.c_int32), ("device", C.c_int32), ("n_graphs", C.c_uint32), ("row_stride", C.c_uint32),
                 ("size", C.c_uint64), ("n_nodes_total", C.c_uint64), ("n_edges_total", C.c_uint64),
-                ("entry_point", C.c_int64), ("device_bytes", C.c_uint64)]
+                ("entry_point", C.c_int64), ("device_bytes", C.c_uint64), ("build_prunes", C.c_uint64),
+                ("build_unlinked", C.c_uint64), ("build_dropped_appends", C.c_uint64)]
 
 
 class SynthParamsC(C.Structure):
@@ -43,7 +44,7 @@ class SynthParamsC(C.Structure):
 
 class BuildParamsC(C.Structure):
     _fields_ = [("ef_construction", C.c_uint32), ("connections", C.c_uint32), ("max_connections", C.c_uint32),
-                ("rayon_threads", C.c_uint32)]
+                ("rayon_threads", C.c_uint32), ("serial_prefix", C.c_uint32)]
 
 
 def build_library(force: bool = False) -> str:

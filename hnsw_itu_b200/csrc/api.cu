@@ -168,6 +168,9 @@ int hb_index_get_info(const hb_index* h, hb_index_info* info) {
     info->n_edges_total = e;
     info->entry_point = idx->ep_file;
     info->device_bytes = idx->device_bytes;
+    info->build_prunes = idx->build_prunes;
+    info->build_unlinked = idx->build_unlinked;
+    info->build_dropped_appends = idx->build_dropped_appends;
   });
 }
 

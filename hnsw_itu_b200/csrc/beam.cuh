@@ -226,7 +226,7 @@ __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint3
     for (uint32_t base = 0; base <= deg; base += 32) {
       const uint32_t wi = base + lane;
       if (base) word = (wi <= deg) ? __ldg(row + wi) : 0u;
-      const bool valid = (wi >= 1u) && (wi <= deg);
+      const bool valid = (wi >= 1u) && (wi <= deg) && word != 0xFFFFFFFFu;  // 0xFFFFFFFF: builder tombstone
       bool isnew = false;
       if (valid) {  // nsw.rs:157-161 through the recently-seen cache
         const uint32_t h = (word * 0x9E3779B1u) >> ws.cache_shift;

@@ -85,6 +85,7 @@ struct Index {
   uint32_t ep_gid = 0;
   uint64_t device_bytes = 0;
   int sm_count = 0;
+  uint64_t build_dropped_appends = 0, build_prunes = 0, build_unlinked = 0;  // builder.cu statistics
   mutable std::mutex mu;  // serialises launches that share the workspace
   mutable SearchWorkspace ws;
   ~Index();

@@ -67,6 +67,9 @@ typedef struct hb_index_info {
   uint64_t n_edges_total; /* directed */
   int64_t entry_point;    /* as stored in the file (index into the top graph), -1 = None */
   uint64_t device_bytes;
+  /* hb_build_hnsw statistics (0 for loaded indexes): M-prunings done (nsw.rs:109-130), edges removed on the far
+   * side by them, and back edges dropped because a row was physically full (should be 0) */
+  uint64_t build_prunes, build_unlinked, build_dropped_appends;
 } hb_index_info;
 
 /* per-query work counters (feature `instrument` of the reference traces V as
@@ -167,6 +170,7 @@ typedef struct hb_build_params {
   uint32_t connections;     /* -m, default 24 */
   uint32_t max_connections; /* -M, default 256 */
   uint32_t rayon_threads;   /* stands in for rayon::current_num_threads(): chunk = 32 * this, and it is mixed into the level seed */
+  uint32_t serial_prefix;   /* points inserted one at a time before chunking starts; 0 = the reference's 50 000 (hnsw.rs:54) */
 } hb_build_params;
 int hb_build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params* p, int device, int keep_host, hb_index** out);
 
