@@ -87,6 +87,9 @@ def lib() -> C.CDLL:
     L.hb_knns.argtypes = [vp, _u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, _u64p, _u64p, _u32p, vp]
     L.hb_search.argtypes = [vp, _u64p, C.c_uint32, C.c_uint32, C.c_uint32, _u64p, _u64p, _u32p]
     L.hb_knns_device.argtypes = [vp, vp, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]
+    L.hb_index_last_search_ms.argtypes = [vp]
+    L.hb_index_last_search_ms.restype = C.c_double
+    L.hb_kernel_launches.restype = C.c_uint64
     L.hb_ground_truth.argtypes = [_u64p, C.c_uint64, _u64p, C.c_uint64, C.c_uint32, C.c_int, _u64p, _u64p]
     L.hb_ground_truth_device.argtypes = [vp, C.c_uint64, C.c_uint64, vp, C.c_uint64, C.c_uint32, vp, vp]
     L.hb_topk_merge_device.argtypes = [vp, C.c_uint32, C.c_uint64, C.c_uint32, vp, vp]

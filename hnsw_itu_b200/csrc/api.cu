@@ -1,6 +1,7 @@
 // api.cu -- the extern "C" surface declared in include/hnsw_b200.h.
 // Every entry point converts exceptions into hb_status codes + a thread-local
 // message; nothing throws across the boundary.
+#include <atomic>
 #include <cstring>
 #include <memory>
 
@@ -11,6 +12,10 @@ namespace {
 thread_local std::string g_last_error;
 }
 void set_last_error(const std::string& m) { g_last_error = m; }
+namespace {
+std::atomic<uint64_t> g_launches{0};
+}
+void count_launches(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 namespace {
 
@@ -57,6 +62,9 @@ extern "C" {
 
 const char* hb_last_error(void) { return g_last_error.c_str(); }
 int hb_version(void) { return HB_VERSION; }
+
+uint64_t hb_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
+double hb_index_last_search_ms(const hb_index* h) { return h ? reinterpret_cast<const Index*>(h)->last_search_ms : 0.0; }
 
 int hb_device_count(int* count) {
   return guarded([&] {
@@ -228,6 +236,41 @@ int hb_knns_device(const hb_index* h, const void* d_queries, uint64_t nq, uint32
   });
 }
 
+namespace hb {
+namespace {
+// take an idle staging set from the index's pool (or make one) and grow it to the call's size
+CallBuffers acquire_buffers(const Index& idx, uint64_t nq, uint32_t k, bool counters) {
+  CallBuffers b;
+  {
+    std::lock_guard<std::mutex> lock(idx.pool_mu);
+    if (!idx.pool.empty()) { b = idx.pool.back(); idx.pool.pop_back(); }
+  }
+  if (!b.stream) HB_CUDA(cudaStreamCreateWithFlags(&b.stream, cudaStreamNonBlocking));
+  if (b.cap_q < nq) {
+    cudaFree(b.q); cudaFree(b.found); cudaFree(b.ctr);
+    b.q = nullptr; b.found = nullptr; b.ctr = nullptr; b.cap_q = 0;
+    HB_CUDA(cudaMalloc(&b.q, nq * 128));
+    HB_CUDA(cudaMalloc(&b.found, nq * 4));
+    HB_CUDA(cudaMalloc(&b.ctr, nq * sizeof(hb_counters)));
+    b.cap_q = nq;
+  }
+  if (b.cap_out < nq * k) {
+    cudaFree(b.keys); cudaFree(b.dists);
+    b.keys = b.dists = nullptr; b.cap_out = 0;
+    HB_CUDA(cudaMalloc(&b.keys, nq * k * 8));
+    HB_CUDA(cudaMalloc(&b.dists, nq * k * 8));
+    b.cap_out = nq * k;
+  }
+  (void)counters;
+  return b;
+}
+void release_buffers(const Index& idx, const CallBuffers& b) {
+  std::lock_guard<std::mutex> lock(idx.pool_mu);
+  idx.pool.push_back(b);
+}
+}  // namespace
+}  // namespace hb
+
 int hb_knns(const hb_index* h, const uint64_t* queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, uint64_t* keys,
             uint64_t* dists, uint32_t* found, hb_counters* counters) {
   return guarded([&] {
@@ -236,18 +279,22 @@ int hb_knns(const hb_index* h, const uint64_t* queries, uint64_t nq, uint32_t k,
     HB_REQUIRE(k >= 1 && k <= HB_MAX_K, HB_ERR_INVALID, "k out of range");
     if (nq == 0) return;
     HB_CUDA(cudaSetDevice(idx->device));
-    DevMem<uint64_t> dq(nq * 16), dk(nq * k), dd(nq * k);
-    DevMem<uint32_t> df(nq);
-    DevMem<hb_counters> dc(counters ? nq : 0);
-    HB_CUDA(cudaMemcpy(dq.p, queries, nq * 128, cudaMemcpyHostToDevice));
-    int rc = hb_knns_device(h, dq.p, nq, k, ef, flags, dk.p, dd.p, df.p, counters ? (void*)dc.p : nullptr, nullptr);
+    CallBuffers b = acquire_buffers(*idx, nq, k, counters != nullptr);
+    struct Release {
+      const Index& i; const CallBuffers& b;
+      ~Release() { release_buffers(i, b); }
+    } release{*idx, b};
+    // pinned caller memory makes these true asynchronous DMA transfers; pageable memory is staged by the driver
+    HB_CUDA(cudaMemcpyAsync(b.q, queries, nq * 128, cudaMemcpyHostToDevice, b.stream));
+    int rc = hb_knns_device(h, b.q, nq, k, ef, flags, b.keys, b.dists, b.found, counters ? (void*)b.ctr : nullptr, b.stream);
     if (rc != HB_OK) throw Error(rc, g_last_error);
-    HB_CUDA(cudaMemcpy(keys, dk.p, nq * k * 8, cudaMemcpyDeviceToHost));
-    HB_CUDA(cudaMemcpy(dists, dd.p, nq * k * 8, cudaMemcpyDeviceToHost));
+    HB_CUDA(cudaMemcpyAsync(keys, b.keys, nq * k * 8, cudaMemcpyDeviceToHost, b.stream));
+    HB_CUDA(cudaMemcpyAsync(dists, b.dists, nq * k * 8, cudaMemcpyDeviceToHost, b.stream));
     std::vector<uint32_t> f(nq);
-    HB_CUDA(cudaMemcpy(f.data(), df.p, nq * 4, cudaMemcpyDeviceToHost));
+    HB_CUDA(cudaMemcpyAsync(f.data(), b.found, nq * 4, cudaMemcpyDeviceToHost, b.stream));
+    if (counters) HB_CUDA(cudaMemcpyAsync(counters, b.ctr, nq * sizeof(hb_counters), cudaMemcpyDeviceToHost, b.stream));
+    HB_CUDA(cudaStreamSynchronize(b.stream));
     if (found) std::memcpy(found, f.data(), nq * 4);
-    if (counters) HB_CUDA(cudaMemcpy(counters, dc.p, nq * sizeof(hb_counters), cudaMemcpyDeviceToHost));
     if (idx->algo == HB_ALGO_BRUTEFORCE) {
       // rows past found are UINT64_MAX from the packed form: zero them / pad like the graph path
       for (uint64_t i = 0; i < nq; ++i)

@@ -151,6 +151,7 @@ void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint3
   HB_CUDA(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   topk_merge_kernel<<<(unsigned)((nq + 3) / 4), 128, smem, stream>>>(static_cast<const uint64_t*>(d_lists), n_lists, nq, k,
                                                                      static_cast<uint64_t*>(d_out));
+    count_launches();
   HB_CUDA(cudaGetLastError());
 }
 
@@ -158,6 +159,7 @@ void unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists
   if (n == 0) return;
   unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(static_cast<const uint64_t*>(d_packed), n,
                                                                  static_cast<uint64_t*>(d_keys), static_cast<uint64_t*>(d_dists));
+    count_launches();
   HB_CUDA(cudaGetLastError());
 }
 
@@ -189,6 +191,7 @@ void ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, co
   scan_topk_kernel<<<(unsigned)((items + kScanWarps - 1) / kScanWarps), kScanWarps * 32, smem, stream>>>(
       static_cast<const uint4*>(d_data), n, key_offset, static_cast<const uint4*>(d_queries), (uint32_t)nq, k, qt, n_qtiles,
       (uint32_t)n_chunks, chunk_rows, partial);
+    count_launches();
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) {
     try {

@@ -201,8 +201,12 @@ __global__ void __launch_bounds__(128) build_apply_kernel(const BuildCtx c, uint
         if (w < c.work_cap) c.work[w] = e; else atomicOr(c.ctr + 9, kErrWork);
       }
     } else {
+      // row e is physically full (a new top layer's star, hnsw.rs:89-92 + nsw.rs:101-103): the reference would have
+      // pruned e before it got here; treat p as pruned by e and unlink the edge on p's side too
       atomicSub(row_e, 1u);
       atomicAdd(c.ctr + 8, 1u);
+      const uint32_t q = atomicAdd(c.ctr + 1, 1u);
+      if (q < c.req_cap) { c.req[2 * (size_t)q] = p; c.req[2 * (size_t)q + 1] = e; } else atomicOr(c.ctr + 9, kErrReq);
     }
   }
 }
@@ -451,6 +455,7 @@ void export_graphs(const Index& idx, const uint64_t* base_data, const std::vecto
     if (!n) continue;
     DevArr<uint32_t> d_deg(n);
     gather_degrees_kernel<<<(unsigned)((n + 255) / 256), 256>>>(idx.d_adj, idx.stride, first, n, d_deg.p);
+    count_launches();
     HB_CUDA(cudaGetLastError());
     std::vector<uint32_t> deg(n);
     HB_CUDA(cudaMemcpy(deg.data(), d_deg.p, n * 4, cudaMemcpyDeviceToHost));
@@ -461,6 +466,7 @@ void export_graphs(const Index& idx, const uint64_t* base_data, const std::vecto
     DevArr<uint32_t> d_ids(hg.ids.size());
     HB_CUDA(cudaMemcpy(d_off.p, hg.off.data(), (n + 1) * 8, cudaMemcpyHostToDevice));
     rows_to_csr_kernel<<<(unsigned)((n * 32 + 255) / 256), 256>>>(idx.d_adj, idx.stride, first, n, (uint32_t)first, d_off.p, d_ids.p);
+    count_launches();
     HB_CUDA(cudaGetLastError());
     HB_CUDA(cudaMemcpy(hg.ids.data(), d_ids.p, hg.ids.size() * 4, cudaMemcpyDeviceToHost));
   }
@@ -591,14 +597,19 @@ Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& bp, i
     const uint32_t blocks = (s.count + kBuildWarps - 1) / kBuildWarps;
     build_descent_kernel<<<blocks, kBuildWarps * 32, smem_descent, stream>>>(c, (uint32_t)s.first, s.count, ep_gid, (int)cur_layers,
                                                                             (int)s.level);
+    count_launches();
     for (int g = (int)s.level; g >= 0; --g) {
       const uint32_t node_first = (uint32_t)(gbase[g] + cur[g]);
       HB_CUDA(cudaMemsetAsync(d_ctr.p, 0, 3 * 4, stream));
       select_kernel<<<blocks, kBuildWarps * 32, smem_select, stream>>>(c, g, node_first, s.count, s.sequential ? 1 : 0);
+    count_launches();
       build_apply_kernel<<<(s.count * 32 + 127) / 128, 128, 0, stream>>>(c, node_first, s.count);
+    count_launches();
       const uint32_t prune_blocks = s.sequential ? 2u : (uint32_t)std::min<uint64_t>((uint64_t)idx->sm_count * 2, work_cap);
       build_prune_kernel<<<prune_blocks, kPruneThreads, smem_prune, stream>>>(c, node_first, node_first + s.count, step_id);
+    count_launches();
       build_unlink_kernel<<<s.sequential ? 4u : (unsigned)idx->sm_count, 128, 0, stream>>>(c);
+    count_launches();
     }
     for (uint32_t g = 0; g <= s.level; ++g) cur[g] += s.count;
     if ((step_id & 1023u) == 0) HB_CUDA(cudaGetLastError());
@@ -614,6 +625,7 @@ Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& bp, i
     if (gsize[g])
       build_compact_kernel<<<(unsigned)((gsize[g] * 32 + 255) / 256), 256, 0, stream>>>(idx->d_adj + gbase[g] * idx->stride, idx->stride,
                                                                                        gsize[g], d_edges.p + g, d_maxdeg.p);
+    count_launches();
   HB_CUDA(cudaGetLastError());
   HB_CUDA(cudaStreamSynchronize(stream));
   uint32_t h_ctr[16];

@@ -18,6 +18,7 @@ struct Error : std::runtime_error {
 };
 
 void set_last_error(const std::string& m);
+void count_launches(uint64_t n = 1);  // every kernel launch of the library is counted (hb_kernel_launches)
 
 #define HB_CUDA(expr)                                                                                     \
   do {                                                                                                    \
@@ -67,6 +68,17 @@ struct SearchWorkspace {
   uint64_t qcap = 0;
 };
 
+// device staging of one hb_knns call with host buffers (pooled on the index: no cudaMalloc on the hot path)
+struct CallBuffers {
+  uint64_t* q = nullptr;   // cap_q * 16
+  uint64_t* keys = nullptr;  // cap_out
+  uint64_t* dists = nullptr; // cap_out
+  uint32_t* found = nullptr; // cap_q
+  hb_counters* ctr = nullptr;  // cap_q
+  uint64_t cap_q = 0, cap_out = 0;
+  cudaStream_t stream = nullptr;
+};
+
 struct Index {
   int device = 0;
   int algo = HB_ALGO_HNSW;
@@ -87,6 +99,10 @@ struct Index {
   int sm_count = 0;
   uint64_t build_dropped_appends = 0, build_prunes = 0, build_unlinked = 0;  // builder.cu statistics
   mutable std::mutex mu;  // serialises launches that share the workspace
+  mutable std::mutex pool_mu;
+  mutable std::vector<CallBuffers> pool;  // idle staging sets
+  mutable cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  mutable double last_search_ms = 0.0;  // device time of the search kernel(s) of the last knns call on this index
   mutable SearchWorkspace ws;
   ~Index();
 };

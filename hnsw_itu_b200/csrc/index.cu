@@ -78,6 +78,12 @@ Index::~Index() {
   cudaFree(ws.ctl);
   cudaFree(ws.qstatus);
   cudaFree(ws.qmap);
+  for (CallBuffers& b : pool) {
+    cudaFree(b.q); cudaFree(b.keys); cudaFree(b.dists); cudaFree(b.found); cudaFree(b.ctr);
+    if (b.stream) cudaStreamDestroy(b.stream);
+  }
+  if (ev0) cudaEventDestroy(ev0);
+  if (ev1) cudaEventDestroy(ev1);
 }
 
 Index* index_from_host(int algo, std::vector<HostGraph>&& graphs, int64_t ep, int device, bool keep_host) {
@@ -157,12 +163,14 @@ Index* index_from_host(int algo, std::vector<HostGraph>&& graphs, int64_t ep, in
       const uint64_t threads = hg.n * 32;
       csr_to_rows_kernel<<<(unsigned)((threads + 255) / 256), 256>>>(d_off.p, d_ids.p, hg.n, (uint32_t)idx->g_base[g], idx->stride,
                                                                      idx->d_adj + idx->g_base[g] * idx->stride);
+    count_launches();
       HB_CUDA(cudaGetLastError());
       if (g > 0) {
         DevBuf<uint64_t> d_dn(hg.n);
         HB_CUDA(cudaMemcpy(d_dn.p, hg.down.data(), hg.n * 8, cudaMemcpyHostToDevice));
         down_to_gid_kernel<<<(unsigned)((hg.n + 255) / 256), 256>>>(d_dn.p, hg.n, (uint32_t)idx->g_base[g - 1],
                                                                    idx->d_down + (idx->g_base[g] - idx->n_base));
+    count_launches();
         HB_CUDA(cudaGetLastError());
         HB_CUDA(cudaDeviceSynchronize());
       }

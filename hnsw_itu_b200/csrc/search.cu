@@ -423,6 +423,8 @@ void ensure_workspace(const Index& idx, uint32_t vcap_log2, uint32_t slots, uint
 void ensure_common(const Index& idx, uint64_t nq) {
   SearchWorkspace& ws = idx.ws;
   if (!ws.ctl) HB_CUDA(cudaMalloc(&ws.ctl, 8 * sizeof(uint32_t)));
+  if (!idx.ev0) HB_CUDA(cudaEventCreate(&idx.ev0));
+  if (!idx.ev1) HB_CUDA(cudaEventCreate(&idx.ev1));
   if (ws.qcap < nq) {
     cudaFree(ws.qstatus);
     cudaFree(ws.qmap);
@@ -456,6 +458,7 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   if (ef == 0) ef = 1;  // nsw.rs:167-176 behaves identically for ef = 0 and ef = 1
 
   std::lock_guard<std::mutex> lock(idx.mu);
+  idx.last_search_ms = 0.0;
   SearchParams p{};
   p.sk = idx.d_sk;
   p.adj = idx.d_adj;
@@ -510,11 +513,19 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     p.qmap = nullptr;
     p.nq = (uint32_t)nq;
     HB_CUDA(cudaMemsetAsync(ws.ctl, 0, 8 * sizeof(uint32_t), stream));
+    HB_CUDA(cudaEventRecord(idx.ev0, stream));
     fl.kernel<<<fblocks, kWarpsPerBlock * 32, fsmem, stream>>>(p, cache_log2);
+    count_launches();
     HB_CUDA(cudaGetLastError());
+    HB_CUDA(cudaEventRecord(idx.ev1, stream));
     uint32_t h_ctl[2] = {0, 0};
     HB_CUDA(cudaMemcpyAsync(h_ctl, ws.ctl, sizeof h_ctl, cudaMemcpyDeviceToHost, stream));
     HB_CUDA(cudaStreamSynchronize(stream));
+    {
+      float ms = 0.f;
+      HB_CUDA(cudaEventElapsedTime(&ms, idx.ev0, idx.ev1));
+      idx.last_search_ms += ms;
+    }
     if (!h_ctl[1]) return;
     // boundary-tie stack overflow (tie-heavy data): rerun exactly those queries on the large-capacity kernel
     h_status.resize(nq);
@@ -541,11 +552,19 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     p.vcap_log2 = ws.vcap_log2;
     p.spill_cap = ws.spill_cap;
     HB_CUDA(cudaMemsetAsync(ws.ctl, 0, 8 * sizeof(uint32_t), stream));
+    HB_CUDA(cudaEventRecord(idx.ev0, stream));
     hnsw_search_kernel<<<blocks, kWarpsPerBlock * 32, smem, stream>>>(p);
+    count_launches();
     HB_CUDA(cudaGetLastError());
+    HB_CUDA(cudaEventRecord(idx.ev1, stream));
     uint32_t h_ctl[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     HB_CUDA(cudaMemcpyAsync(h_ctl, ws.ctl, sizeof h_ctl, cudaMemcpyDeviceToHost, stream));
     HB_CUDA(cudaStreamSynchronize(stream));
+    {
+      float ms = 0.f;
+      HB_CUDA(cudaEventElapsedTime(&ms, idx.ev0, idx.ev1));
+      idx.last_search_ms += ms;
+    }
 #ifdef HB_DEBUG_BOUNDS
     HB_REQUIRE(h_ctl[2] == 0, HB_ERR_INTERNAL,
                "bounds check " + std::to_string(h_ctl[2]) + " value " + std::to_string(h_ctl[3]) + " query " + std::to_string(h_ctl[4]) +

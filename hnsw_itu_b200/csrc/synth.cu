@@ -81,10 +81,12 @@ void synth_device(const hb_synth_params& p, uint64_t start, uint64_t n, void* d_
   const uint32_t count = p.distinct_planes * p.latent_dim;
   HB_CUDA(cudaMallocAsync(&planes, (size_t)count * 2, stream));
   planes_kernel<<<(count + 255) / 256, 256, 0, stream>>>(stream_key(p.seed_planes, 0), count, planes);
+    count_launches();
   const uint64_t blocks = (n + kRowsPerBlock - 1) / kRowsPerBlock;
   synth_kernel<<<(unsigned)blocks, 256, (size_t)kRowsPerBlock * p.latent_dim * 4, stream>>>(
       p, stream_key(p.seed_centres, 0), stream_key(p.seed_rows, 0), stream_key(p.seed_rows, 1), planes, start, n,
       static_cast<uint64_t*>(d_out));
+    count_launches();
   cudaError_t e = cudaGetLastError();
   cudaFreeAsync(planes, stream);
   HB_CUDA(e);

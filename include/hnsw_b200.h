@@ -134,6 +134,12 @@ int hb_search(const hb_index* idx, const uint64_t* query, uint32_t k, uint32_t e
 int hb_knns_device(const hb_index* idx, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags,
                    void* d_keys, void* d_dists, void* d_found, void* d_counters, void* stream);
 
+/* Device time (ms, CUDA events on the launching stream) of the search kernel(s) of the last hb_knns* call on this
+ * index; used for the roofline figure. */
+double hb_index_last_search_ms(const hb_index* idx);
+/* Number of CUDA kernels this library has launched in this process so far. */
+uint64_t hb_kernel_launches(void);
+
 /* ---- brute force / ground truth ----------------------------------------------- */
 
 /* `ground-truth` (cli/src/main.rs:715-754): Bruteforce::search
