@@ -1,0 +1,18 @@
+#!/bin/bash
+# Runs on the GPU box (under gpurun): the plain bench first, then the ncu launch list of the same command
+# (index-construction kernels filtered out by name: ~350 k launches that are outside the timed region) and one
+# `--set full` capture of the search kernel.  Outputs land in gpurun_out/; summaries are copied to profiles/ by hand.
+set -u
+tag="${1:-r01}"
+shift || true
+cmd="python bench.py --steps 3 --warmup 3 --no-cpu-baseline $*"
+out=gpurun_out
+mkdir -p $out
+$cmd > $out/bench_plain_$tag.json 2> $out/bench_plain_$tag.err || { echo "plain run failed"; tail -5 $out/bench_plain_$tag.err; exit 1; }
+cat $out/bench_plain_$tag.json
+ncu --metrics gpu__time_duration.sum --clock-control none -k 'regex:hnsw_search|scan_topk|topk_merge|unpack|synth|gt_' -c 400 \
+    --csv --log-file $out/launches_$tag.csv $cmd > $out/ncu_launches_$tag.log 2>&1
+echo "launch list rc=$?"
+ncu --set full --clock-control none --import-source on -k 'regex:hnsw_search' -s 4 -c 2 -f -o $out/search_$tag $cmd > $out/ncu_full_$tag.log 2>&1
+echo "full capture rc=$?"
+ls -la $out
