@@ -10,7 +10,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhnswb200.so")
+LIB_PATH = os.environ.get("HB_LIB_PATH") or os.path.join(_HERE, "libhnswb200.so")  # HB_LIB_PATH: A/B builds (tools/ab.py)
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "hnsw_b200.h")
 
 HB_OK = 0

@@ -31,6 +31,8 @@ namespace hb {
 
 constexpr uint32_t kFullMask = 0xFFFFFFFFu;
 constexpr uint64_t kBeamInf = ~0ull;  // empty slot: larger than any element, expanded bit set
+constexpr uint32_t kIdsCap = 64;      // ids staged per segment = two 128-B lines of an adjacency row
+constexpr uint32_t kNoKey = 0xFFFFFFFFu;
 
 __device__ __forceinline__ uint64_t bm_pack(uint32_t d, uint32_t key) { return ((uint64_t)d << 33) | ((uint64_t)key << 1); }
 __device__ __forceinline__ uint32_t bm_dist(uint64_t v) { return (uint32_t)(v >> 33); }
@@ -55,7 +57,7 @@ struct SearchCounters {
 struct WarpScratch {
   uint32_t* cache;       // 1 << cache_log2 recently seen ids (0xFFFFFFFF = empty)
   uint32_t cache_shift;  // 32 - cache_log2
-  uint32_t* ids;         // 32 staged neighbour ids
+  uint32_t* ids;         // kIdsCap staged neighbour ids (one two-line segment of an adjacency row, compacted)
 };
 
 template <int R>
@@ -111,6 +113,39 @@ struct BeamRegs {
     if (maxv == c) maxv = c | 1ull;
     key = bm_key(c);
     return true;
+  }
+
+  // the element pop_unexpanded() would return next, without marking it (used to predict the next expansion)
+  __device__ __forceinline__ bool peek_unexpanded(uint32_t& key) const {
+    uint64_t cv = kBeamInf;
+#pragma unroll
+    for (int r = R - 1; r >= 0; --r)
+      if (!(w[r] & 1ull)) cv = w[r];
+    const uint32_t m = __ballot_sync(kFullMask, cv != kBeamInf);
+    if (!m) return false;
+    key = __shfl_sync(kFullMask, bm_key(cv), __ffs(m) - 1);
+    return true;
+  }
+
+  // the next two elements pop_unexpanded() would return if nothing were inserted in between (kNoKey = none)
+  __device__ __forceinline__ void peek_unexpanded2(uint32_t& k1, uint32_t& k2) const {
+    uint64_t c1 = kBeamInf;
+#pragma unroll
+    for (int r = R - 1; r >= 0; --r)
+      if (!(w[r] & 1ull)) c1 = w[r];
+    const uint32_t m = __ballot_sync(kFullMask, c1 != kBeamInf);
+    k1 = k2 = kNoKey;
+    if (!m) return;
+    const uint32_t l1 = __ffs(m) - 1;
+    const uint64_t first = __shfl_sync(kFullMask, c1, l1);
+    k1 = bm_key(first);
+    uint64_t c2 = kBeamInf;
+#pragma unroll
+    for (int r = R - 1; r >= 0; --r)
+      if (!(w[r] & 1ull) && w[r] > first) c2 = w[r];
+    const uint32_t m2 = __ballot_sync(kFullMask, c2 != kBeamInf);
+    if (!m2) return;
+    k2 = __shfl_sync(kFullMask, bm_key(c2), __ffs(m2) - 1);
   }
 
   // w.push(v); if |w| > ef: w.pop_max()  (nsw.rs:171-176).  Precondition: v not in w, and (size < ef or v < maxv).
@@ -190,13 +225,66 @@ __device__ __forceinline__ void cache_clear(const WarpScratch& ws) {
   __syncwarp();
 }
 
+// ---- prefetch policy (compile-time switches so variants can be A/B-timed on the B200) ----
+//   HB_PREFETCH_ROW: 0 = off; 1 = the adjacency row of the predicted next candidate is loaded into registers
+//                    one expansion ahead; 2 = additionally the row of the predicted second-next candidate is
+//                    prefetched into L2 (so that the register load one expansion later is an L2 hit)
+//   HB_PREFETCH_SK : 0 = off; n = n L2 prefetches (32-B sector stride 128/n B) per sketch row of the predicted next
+//                    candidate's neighbours
+#ifndef HB_PREFETCH_ROW
+#define HB_PREFETCH_ROW 0
+#endif
+#ifndef HB_PREFETCH_SK
+#define HB_PREFETCH_SK 0
+#endif
+
+// HB_DIAG_CLOCK (diagnostics build only): the counters are replaced by cycles spent per phase
+// X = waiting for the adjacency row, E = cache check + compaction, V = sketch gather + reduction, A = accept replay
+#ifdef HB_DIAG_CLOCK
+#define HB_TICK(var) const long long var = clock64()
+#define HB_ACC(field, t0, t1) (field) += (uint32_t)((t1) - (t0))
+#else
+#define HB_TICK(var) do {} while (0)
+#define HB_ACC(field, t0, t1) do {} while (0)
+#endif
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// Prefetch (into L2) the sketches of the neighbours held in the two row words w0 (row words 0..31) / w1 (32..63).
+__device__ __forceinline__ void prefetch_row_sketches(const uint4* __restrict__ sk, uint32_t w0, uint32_t w1) {
+#if HB_PREFETCH_SK > 0
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t ndeg = __shfl_sync(kFullMask, w0, 0);
+  const bool v0 = lane >= 1u && lane <= ndeg && w0 != kNoKey;
+  const bool v1 = 32u + lane <= ndeg && w1 != kNoKey;
+#pragma unroll
+  for (int i = 0; i < HB_PREFETCH_SK; ++i) {
+    if (v0) prefetch_l2(reinterpret_cast<const char*>(sk + (size_t)w0 * 8) + i * (128 / HB_PREFETCH_SK));
+    if (v1) prefetch_l2(reinterpret_cast<const char*>(sk + (size_t)w1 * 8) + i * (128 / HB_PREFETCH_SK));
+  }
+#endif
+}
+
 // nsw::search(graph, q, ef, ep) (nsw.rs:133-184) on the graph that contains gid `ep`.  On return b holds w.
 // status != 0: the boundary-tie stack overflowed (the caller reruns the query on the large-capacity path).
+//
+// One expansion = one adjacency row, handled in SEGMENTS of two 128-B lines (64 row words): both lines are loaded
+// together, every neighbour is tested against the recently-seen cache, the unseen ids of the whole segment are
+// compacted IN NEIGHBOUR ORDER into ws.ids, and dense groups of 32 go through hamming32() + the sequential accept
+// replay.  Rows must have a stride of at least 64 words (index.cu guarantees it).
+//
+// Latency hiding: the reference's loop is a chain of dependent random reads (row -> sketches -> accept -> next row).
+// After popping candidate c_t the beam already names the most likely c_{t+1} (its next unexpanded element) and
+// c_{t+2}; c_{t+1}'s row is loaded into registers now and consumed one expansion later, c_{t+2}'s row is prefetched
+// into L2, and once c_{t+1}'s row words have arrived the sketches of its neighbours are prefetched into L2.  A wrong
+// prediction (a neighbour accepted in this expansion overtakes them) falls back to plain loads; results never
+// depend on the prediction.
 template <int R>
 __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint32_t ef, uint32_t ep, const WarpScratch& ws,
                                             uint32_t* spill, uint32_t spill_cap, BeamRegs<R>& b, SearchCounters& c,
                                             uint32_t& status) {
   const uint32_t lane = threadIdx.x & 31;
+  const uint32_t lt_mask = (1u << lane) - 1u;
   {
     const uint32_t d0 = hamming1(gv.sk, ep, qv);  // nsw.rs:140-141
     if (lane == 0) ws.cache[(ep * 0x9E3779B1u) >> ws.cache_shift] = ep;  // nsw.rs:143-144
@@ -204,6 +292,7 @@ __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint3
     ++c.V;
     __syncwarp();
   }
+  uint32_t pkey = kNoKey, pw0 = 0, pw1 = 0;  // predicted next candidate and the first two lines of its row
   for (;;) {
     // ---- c = cands.pop_min(); if c.distance > F break  (nsw.rs:148-154) ----
     uint32_t ckey;
@@ -217,56 +306,135 @@ __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint3
         break;
       }
     }
+#ifndef HB_DIAG_CLOCK
     ++c.X;
+#endif
+    HB_TICK(t_row0);
     // ---- for e in graph.neighborhood(c.key)  (nsw.rs:156) ----
     const uint32_t* row = gv.adj + (size_t)ckey * gv.stride;
-    uint32_t word = __ldg(row + lane);
-    const uint32_t deg = __shfl_sync(kFullMask, word, 0);
-    c.E += deg;
-    for (uint32_t base = 0; base <= deg; base += 32) {
-      const uint32_t wi = base + lane;
-      if (base) word = (wi <= deg) ? __ldg(row + wi) : 0u;
-      const bool valid = (wi >= 1u) && (wi <= deg) && word != 0xFFFFFFFFu;  // 0xFFFFFFFF: builder tombstone
-      bool isnew = false;
-      if (valid) {  // nsw.rs:157-161 through the recently-seen cache
-        const uint32_t h = (word * 0x9E3779B1u) >> ws.cache_shift;
-        isnew = ws.cache[h] != word;
-        if (isnew) ws.cache[h] = word;
+    uint32_t w0, w1;
+    if (ckey == pkey) {
+      w0 = pw0;
+      w1 = pw1;
+#ifdef HB_DIAG_PRED
+      c.A += 1u << 16;  // diagnostics build: prediction hits in the high half of A
+#endif
+    } else {
+      w0 = __ldg(row + lane);
+      w1 = __ldg(row + 32 + lane);
+    }
+#if HB_PREFETCH_ROW > 0
+    {
+      uint32_t n1 = kNoKey, n2 = kNoKey;
+      b.peek_unexpanded2(n1, n2);
+      pkey = n1;
+      if (n1 != kNoKey) {
+        const uint32_t* nrow = gv.adj + (size_t)n1 * gv.stride;
+        pw0 = __ldg(nrow + lane);
+        pw1 = __ldg(nrow + 32 + lane);
       }
-      const uint32_t nm = __ballot_sync(kFullMask, isnew);
-      if (!nm) continue;
-      const uint32_t n_new = __popc(nm);
+#if HB_PREFETCH_ROW > 1
+      if (n2 != kNoKey && lane < 2) prefetch_l2(gv.adj + (size_t)n2 * gv.stride + lane * 32);
+#endif
+    }
+#endif
+    const uint32_t deg = __shfl_sync(kFullMask, w0, 0);
+    HB_TICK(t_row1);
+    HB_ACC(c.X, t_row0, t_row1);
+#ifndef HB_DIAG_CLOCK
+    c.E += deg;
+#endif
+    bool sk_done = (pkey == kNoKey);
+    for (uint32_t base = 0; base <= deg; base += 64) {
+      // rows longer than one segment: fetch the next segment's words before working on this one
+      uint32_t nw0 = 0, nw1 = 0;
+      if (base + 64 <= deg) {
+        if (base + 64 + lane <= deg) nw0 = __ldg(row + base + 64 + lane);
+        if (base + 96 + lane <= deg) nw1 = __ldg(row + base + 96 + lane);
+      }
+      // ---- nsw.rs:157-161 through the recently-seen cache; order-preserving compaction of the unseen ids ----
+      HB_TICK(t_chk0);
+      uint32_t n_new;
+      {
+        const uint32_t wi = base + lane;
+        const bool valid = (wi >= 1u) && (wi <= deg) && w0 != kNoKey;  // 0xFFFFFFFF: builder tombstone
+        bool isnew = false;
+        if (valid) {
+          const uint32_t h = (w0 * 0x9E3779B1u) >> ws.cache_shift;
+          isnew = ws.cache[h] != w0;
+          if (isnew) ws.cache[h] = w0;
+        }
+        const uint32_t nm = __ballot_sync(kFullMask, isnew);
+        if (isnew) ws.ids[__popc(nm & lt_mask)] = w0;
+        n_new = __popc(nm);
+      }
+      if (base + 32 <= deg) {
+        const uint32_t wi = base + 32 + lane;
+        const bool valid = (wi <= deg) && w1 != kNoKey;
+        bool isnew = false;
+        if (valid) {
+          const uint32_t h = (w1 * 0x9E3779B1u) >> ws.cache_shift;
+          isnew = ws.cache[h] != w1;
+          if (isnew) ws.cache[h] = w1;
+        }
+        const uint32_t nm = __ballot_sync(kFullMask, isnew);
+        if (isnew) ws.ids[n_new + __popc(nm & lt_mask)] = w1;
+        n_new += __popc(nm);
+      }
+#ifndef HB_DIAG_CLOCK
       c.V += n_new;
-      if (isnew) ws.ids[__popc(nm & ((1u << lane) - 1u))] = word;  // order-preserving compaction
+#endif
       __syncwarp();
-      const uint32_t myid = ws.ids[lane < n_new ? lane : 0];
-      const uint32_t myd = hamming32(gv.sk, ws.ids, n_new, qv);  // nsw.rs:164-165
-      __syncwarp();
-      // ---- sequential accept in neighbour order (nsw.rs:162-176) ----
-      bool active = lane < n_new;
-      for (;;) {
-        const bool pass = active && (b.size < ef || myd < b.F());  // !(d >= F && |w| >= ef)
-        const uint32_t pm = __ballot_sync(kFullMask, pass);
-        if (!pm) break;
-        const int first = __ffs(pm) - 1;
-        active = active && ((int)lane > first);
-        const uint64_t v = bm_pack(__shfl_sync(kFullMask, myd, first), __shfl_sync(kFullMask, myid, first));
-        if (b.contains(v)) continue;  // a revisit the cache no longer remembered
-        ++c.A;
-        const uint64_t ev = b.insert(v, ef);
-        if (ev != kBeamInf && !(ev & 1ull) && bm_dist(ev) == b.F()) {
-          // evicted before it was expanded and still tied with the worst distance: it stays a live candidate
-          if (b.spill_n && b.spill_d != b.F()) b.spill_n = 0;
-          b.spill_d = b.F();
-          if (b.spill_n < spill_cap) {
-            if (lane == 0) spill[b.spill_n] = bm_key(ev);
-            ++b.spill_n;
-          } else {
-            status = 2;
+      HB_TICK(t_chk1);
+      HB_ACC(c.E, t_chk0, t_chk1);
+      for (uint32_t g0 = 0; g0 < n_new; g0 += 32) {
+        const uint32_t n = min(32u, n_new - g0);
+        HB_TICK(t_g0);
+        const uint32_t myid = ws.ids[g0 + (lane < n ? lane : 0u)];
+        const uint32_t myd = hamming32(gv.sk, ws.ids + g0, n, qv);  // nsw.rs:164-165
+        if (!sk_done) {
+          prefetch_row_sketches(gv.sk, pw0, pw1);
+          sk_done = true;
+        }
+#ifdef HB_DIAG_CLOCK
+        const long long t_g1 = (myd != 0xFFFFFFFFu) ? clock64() : 0;  // depends on the distances: read after they arrived
+        HB_ACC(c.V, t_g0, t_g1);
+#endif
+        // ---- sequential accept in neighbour order (nsw.rs:162-176) ----
+        bool active = lane < n;
+        for (;;) {
+          const bool pass = active && (b.size < ef || myd < b.F());  // !(d >= F && |w| >= ef)
+          const uint32_t pm = __ballot_sync(kFullMask, pass);
+          if (!pm) break;
+          const int first = __ffs(pm) - 1;
+          active = active && ((int)lane > first);
+          const uint64_t v = bm_pack(__shfl_sync(kFullMask, myd, first), __shfl_sync(kFullMask, myid, first));
+          if (b.contains(v)) continue;  // a revisit the cache no longer remembered
+#ifndef HB_DIAG_CLOCK
+          ++c.A;
+#endif
+          const uint64_t ev = b.insert(v, ef);
+          if (ev != kBeamInf && !(ev & 1ull) && bm_dist(ev) == b.F()) {
+            // evicted before it was expanded and still tied with the worst distance: it stays a live candidate
+            if (b.spill_n && b.spill_d != b.F()) b.spill_n = 0;
+            b.spill_d = b.F();
+            if (b.spill_n < spill_cap) {
+              if (lane == 0) spill[b.spill_n] = bm_key(ev);
+              ++b.spill_n;
+            } else {
+              status = 2;
+            }
           }
         }
+#ifdef HB_DIAG_CLOCK
+        { HB_TICK(t_a1); HB_ACC(c.A, t_g1, t_a1); }
+#endif
       }
+      __syncwarp();  // ws.ids is rewritten by the next segment
+      w0 = nw0;
+      w1 = nw1;
     }
+    if (!sk_done) prefetch_row_sketches(gv.sk, pw0, pw1);
     if (status) break;
   }
 }

@@ -133,7 +133,7 @@ Index* index_from_host(int algo, std::vector<HostGraph>&& graphs, int64_t ep, in
     HB_REQUIRE((uint64_t)ep < graphs[G - 1].n, HB_ERR_FORMAT, "entry point out of range");
     idx->ep_gid = (uint32_t)(idx->g_base[G - 1] + (uint64_t)ep);
   }
-  idx->stride = (uint32_t)(((max_deg + 1) + 31) / 32 * 32);
+  idx->stride = std::max<uint32_t>(64u, (uint32_t)(((max_deg + 1) + 31) / 32 * 32));  // >= 2 lines: the search loads two per expansion
 
   cudaDeviceProp prop;
   HB_CUDA(cudaGetDeviceProperties(&prop, device));

@@ -324,17 +324,20 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) hnsw_search_kernel(con
 // ---------------------------------------------------------------------------------------------
 constexpr uint32_t kFastSpillCap = 64;
 
+#ifndef HB_MIN_BLOCKS
+#define HB_MIN_BLOCKS 6
+#endif
 template <int R>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) hnsw_search_fast_kernel(const SearchParams p, uint32_t cache_log2) {
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS) hnsw_search_fast_kernel(const SearchParams p, uint32_t cache_log2) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const size_t per_warp = ((size_t)4 << cache_log2) + 32 * 4 + kFastSpillCap * 4;
+  const size_t per_warp = ((size_t)4 << cache_log2) + kIdsCap * 4 + kFastSpillCap * 4;
   unsigned char* mine = smem_raw + wib * per_warp;
   WarpScratch ws;
   ws.cache = reinterpret_cast<uint32_t*>(mine);
   ws.cache_shift = 32u - cache_log2;
   ws.ids = reinterpret_cast<uint32_t*>(mine + ((size_t)4 << cache_log2));
-  uint32_t* const spill = ws.ids + 32;
+  uint32_t* const spill = ws.ids + kIdsCap;
   const GraphView gv{p.sk, p.adj, p.stride};
   const uint32_t sub = lane & 7u;
 
@@ -500,7 +503,7 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     static const int env_cache = std::getenv("HB_CACHE_LOG2") ? std::atoi(std::getenv("HB_CACHE_LOG2")) : 0;
     uint32_t cache_log2 = env_cache >= 5 && env_cache <= 13 ? (uint32_t)env_cache : 10u;
     const FastLaunch fl = fast_kernel_for(ef);
-    const size_t fsmem = (size_t)kWarpsPerBlock * (((size_t)4 << cache_log2) + 32 * 4 + kFastSpillCap * 4);
+    const size_t fsmem = (size_t)kWarpsPerBlock * (((size_t)4 << cache_log2) + kIdsCap * 4 + kFastSpillCap * 4);
     HB_CUDA(cudaFuncSetAttribute(fl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
     int fbps = 0;
     HB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fbps, fl.kernel, kWarpsPerBlock * 32, fsmem));
