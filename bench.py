@@ -186,16 +186,24 @@ def main():
     want_cpu = (not a.no_cpu_baseline) and world == 1 and rank == 0
 
     # ---- setup (untimed): data, index, queries, ground truth -------------------------------------------------
-    d_data, data, idx, build_s = build_index(hb, torch, a, keep_host=want_cpu)
-    if not want_cpu:
-        del data
+    # N > 1: rank 0 builds the index once and its arrays are broadcast over NCCL/NVLink (replicated index); every rank
+    # then searches its own batch of nq queries with no data-path collective.
+    from hnsw_itu_b200 import sharded
     dq = synth_on_device(hb, torch, a.nq, 1004 + rank)
-    gt = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
-    _lib.check(lib.hb_ground_truth_device(d_data.data_ptr(), a.n, 0, dq.data_ptr(), a.nq, a.k, gt.data_ptr(), None))
-    torch.cuda.synchronize()
-    gt_keys = gt.cpu().numpy().view(np.uint64) & np.uint64(0xFFFFFFFF)
-    del d_data, gt
-    torch.cuda.empty_cache()
+    idx, build_s, gt_keys, data = None, 0.0, None, None
+    if rank == 0:
+        d_data, data, idx, build_s = build_index(hb, torch, a, keep_host=want_cpu or world > 1)
+        if not want_cpu:
+            del data
+        gt = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
+        _lib.check(lib.hb_ground_truth_device(d_data.data_ptr(), a.n, 0, dq.data_ptr(), a.nq, a.k, gt.data_ptr(), None))
+        torch.cuda.synchronize()
+        gt_keys = gt.cpu().numpy().view(np.uint64) & np.uint64(0xFFFFFFFF)
+        del d_data, gt
+        torch.cuda.empty_cache()
+    t_b = time.time()
+    idx = sharded.broadcast_index(idx, src=0)
+    bcast_s = time.time() - t_b
     dk = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
     dd = torch.empty_like(dk)
     df = torch.empty(a.nq, dtype=torch.int32, device="cuda")
@@ -210,7 +218,7 @@ def main():
     gpu_keys = dk.cpu().numpy().view(np.uint64).copy()
     gpu_dists = dd.cpu().numpy().view(np.uint64).copy()
     ctr = dc.cpu().numpy().astype(np.float64)
-    recall = recall_at_k(gpu_keys, gt_keys, a.k)
+    recall = recall_at_k(gpu_keys, gt_keys, a.k) if rank == 0 else None
 
     # ---- device-resident timing -------------------------------------------------------------------------------
     for _ in range(max(a.warmup, 3)):
@@ -315,7 +323,7 @@ def main():
         "dtype": "u64 xor+popcount (integer exact)", "data": "synthetic",
         "config": {"workload": workload_name(a), "recall_at_10": recall, "l2": "inputs larger than L2: the index is "
                    f"{idx.info().device_bytes / 1e9:.1f} GB and one step gathers {bytes_q * a.nq / 1e9:.2f} GB",
-                   "index_build_s": build_s, "parallelism": "replicated index, one query batch per GPU" if world > 1 else "1 GPU",
+                   "index_build_s": build_s, "index_broadcast_s": bcast_s if world > 1 else None, "parallelism": "replicated index (built on rank 0, broadcast over NCCL), one query batch per GPU, no data-path collective" if world > 1 else "1 GPU",
                    "per_query": {"expansions": X, "ids_scanned": E, "visited_reference": V, "distance_evals_gpu": Vgpu}},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": "hnsw_search_fast_kernel<2>", "kernel_ms": k_ms, "bytes_per_query": bytes_q,

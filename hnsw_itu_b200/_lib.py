@@ -94,6 +94,7 @@ def lib() -> C.CDLL:
     L.hb_ground_truth_device.argtypes = [vp, C.c_uint64, C.c_uint64, vp, C.c_uint64, C.c_uint32, vp, vp]
     L.hb_topk_merge_device.argtypes = [vp, C.c_uint32, C.c_uint64, C.c_uint32, vp, vp]
     L.hb_unpack_device.argtypes = [vp, C.c_uint64, vp, vp, vp]
+    L.hb_pack_device.argtypes = [vp, vp, vp, C.c_uint64, C.c_uint32, C.c_uint64, vp, vp]
     L.hb_synth_device.argtypes = [C.POINTER(SynthParamsC), C.c_uint64, C.c_uint64, vp, vp]
     L.hb_build_hnsw.argtypes = [_u64p, C.c_uint64, C.POINTER(BuildParamsC), C.c_int, C.c_int, C.POINTER(vp)]
     _lib = L

@@ -338,6 +338,15 @@ int hb_unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dis
   });
 }
 
+int hb_pack_device(const void* d_keys, const void* d_dists, const void* d_found, uint64_t nq, uint32_t k, uint64_t key_offset,
+                   void* d_packed, void* stream) {
+  return guarded([&] {
+    HB_REQUIRE(nq == 0 || (d_keys && d_dists && d_found && d_packed), HB_ERR_INVALID, "null device buffer");
+    HB_REQUIRE(k >= 1 && k <= HB_MAX_K, HB_ERR_INVALID, "k out of range");
+    pack_device(d_keys, d_dists, d_found, nq, k, key_offset, d_packed, static_cast<cudaStream_t>(stream));
+  });
+}
+
 int hb_ground_truth(const uint64_t* data, uint64_t n, const uint64_t* queries, uint64_t nq, uint32_t k, int device, uint64_t* keys,
                     uint64_t* dists) {
   return guarded([&] {

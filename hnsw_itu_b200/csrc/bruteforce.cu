@@ -141,7 +141,28 @@ __global__ void unpack_kernel(const uint64_t* __restrict__ packed, uint64_t n, u
   dists[i] = (v == kNone) ? kNone : (v >> 32);
 }
 
+// (keys, dists, found) of a per-shard graph search -> packed ascending lists with global keys (entries past found = none)
+__global__ void pack_kernel(const uint64_t* __restrict__ keys, const uint64_t* __restrict__ dists, const uint32_t* __restrict__ found,
+                            uint64_t nq, uint32_t k, uint64_t key_offset, uint64_t* __restrict__ packed) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq * k) return;
+  const uint64_t q = i / k;
+  const uint32_t j = (uint32_t)(i % k);
+  packed[i] = (j < found[q]) ? ((dists[i] << 32) | (keys[i] + key_offset)) : kNone;
+}
+
 }  // namespace
+
+void pack_device(const void* d_keys, const void* d_dists, const void* d_found, uint64_t nq, uint32_t k, uint64_t key_offset,
+                 void* d_packed, cudaStream_t stream) {
+  if (nq == 0) return;
+  const uint64_t n = nq * k;
+  pack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(static_cast<const uint64_t*>(d_keys), static_cast<const uint64_t*>(d_dists),
+                                                               static_cast<const uint32_t*>(d_found), nq, k, key_offset,
+                                                               static_cast<uint64_t*>(d_packed));
+  count_launches();
+  HB_CUDA(cudaGetLastError());
+}
 
 void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream) {
   HB_REQUIRE(k >= 1 && k <= HB_MAX_K, HB_ERR_INVALID, "k out of range");

@@ -124,6 +124,8 @@ void ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, co
                          void* d_packed, cudaStream_t stream);
 void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream);
 void unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists, cudaStream_t stream);
+void pack_device(const void* d_keys, const void* d_dists, const void* d_found, uint64_t nq, uint32_t k, uint64_t key_offset,
+                 void* d_packed, cudaStream_t stream);
 
 // synth.cu
 void synth_device(const hb_synth_params& p, uint64_t start, uint64_t n, void* d_out, cudaStream_t stream);

@@ -160,6 +160,12 @@ int hb_ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, 
  * (n_lists, nq, k) packed u64 -> (nq, k) packed (new for sharding; the order
  * is total so the merge equals a global Bruteforce + sort). */
 int hb_topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_packed_out, void* stream);
+/* Per-shard graph-search results (hb_knns_device outputs on a shard whose first row has global key
+ * `key_offset`, the reference's `index -b start -l len` sub-range, cli/src/main.rs:596-602,136-140) -> packed
+ * ascending lists with global keys, ready for an all-gather + hb_topk_merge_device.  Entries past found[i] become
+ * UINT64_MAX. */
+int hb_pack_device(const void* d_keys, const void* d_dists, const void* d_found, uint64_t nq, uint32_t k, uint64_t key_offset,
+                   void* d_packed, void* stream);
 /* packed (nq,k) -> keys, dists u64 (UINT64_MAX entries stay UINT64_MAX in both) */
 int hb_unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists, void* stream);
 

@@ -223,3 +223,39 @@ def test_size_independent_properties(hb, oracle):
     gk, gd = hb.ground_truth(data, q[:32], 10)
     assert (gk[:, 0] == np.arange(32)).all() and (gd[:, 0] == 0).all()
     assert (np.diff(((gd << np.uint64(32)) | gk).astype(np.int64), axis=1) > 0).all()
+
+
+def test_sharded_hnsw_pack_and_merge(hb, oracle):
+    """config 5's shape on one GPU: one index per row range (the reference's `index -b start -l len`), same ef on every
+    shard, local keys shifted by the shard offset (hb_pack_device), exact merge == merge of the oracle's per-shard lists.
+    k > found on small shards exercises the "no element" padding."""
+    import torch
+    from hnsw_itu_b200 import sharded
+    data = oracle.synth(9000, 91)
+    q = oracle.synth(120, 92)
+    k, ef = 10, 24
+    bounds = sharded.shard_bounds(len(data), 3)
+    bounds[-1] = (bounds[-1][0], 6)          # a shard with fewer than k rows
+    dq = torch.from_numpy(q.view(np.int64)).cuda()
+    lists = torch.empty((len(bounds), len(q), k), dtype=torch.int64, device="cuda")
+    expect = []
+    for s, (start, ln) in enumerate(bounds):
+        oidx = oracle.build(data[start:start + ln], "hnsw", efc=32, m=8, M=24, parallel=False)
+        hidx = _to_gpu(hb, oidx, keep_host=False)
+        lists[s] = sharded.knns_sharded(hidx, start, dq, k, ef)   # world 1: pack + merge of a single list
+        ok, od, of = oidx.knns(q, k, ef)
+        pk = (od.astype(np.uint64) << np.uint64(32)) | (ok + np.uint64(start))
+        pk[np.arange(k)[None, :] >= of[:, None]] = np.uint64(2**64 - 1)
+        expect.append(pk)
+        assert np.array_equal(lists[s].cpu().numpy().view(np.uint64), pk)
+    merged = sharded.merge_lists_device(lists)
+    keys, dists = sharded.unpack_device(merged)
+    torch.cuda.synchronize()
+    want = np.sort(np.concatenate(expect, axis=1), axis=1)[:, :k]
+    assert np.array_equal(merged.cpu().numpy().view(np.uint64), want)
+    assert np.array_equal(keys.cpu().numpy().view(np.uint64), want & np.uint64(0xFFFFFFFF))
+    # sharded ground truth through the same host function (world 1)
+    dd = torch.from_numpy(data.view(np.int64)).cuda()
+    gt = sharded.ground_truth_sharded(dd, 0, dq, k)
+    gk, gd = oracle.ground_truth(data, q, k)
+    assert np.array_equal(gt.cpu().numpy().view(np.uint64), (gd << np.uint64(32)) | gk)
