@@ -53,12 +53,32 @@ struct SearchCounters {
   uint32_t X = 0, E = 0, V = 0, A = 0;
 };
 
-// per-warp scratch in shared memory
+// How hamming32() fetches sketch rows: 1 = cp.async (LDGSTS) 16 B per lane into a 4-KB shared-memory stage, then LDS
+// (measured on B200, profiles/r01c_gather_shape_microbench.log: a dependent 32-row gather costs 2 040 cycles this way
+// against 2 880 with eight LDG.128 per lane, and it needs no 32 data registers); 0 = LDG.128 into registers.
+#ifndef HB_GATHER_CPASYNC
+#define HB_GATHER_CPASYNC 1
+#endif
+constexpr uint32_t kStageBytes = HB_GATHER_CPASYNC ? 32u * 128u : 0u;
+
+// per-warp scratch in shared memory: [stage 4 KB][cache 4 << cache_log2][ids kIdsCap * 4]
 struct WarpScratch {
+  uint4* stage;          // 32 sketch rows (cp.async destination); lane (g, s) only ever touches rows 4j+g, piece s
   uint32_t* cache;       // 1 << cache_log2 recently seen ids (0xFFFFFFFF = empty)
   uint32_t cache_shift;  // 32 - cache_log2
   uint32_t* ids;         // kIdsCap staged neighbour ids (one two-line segment of an adjacency row, compacted)
 };
+__host__ __device__ constexpr size_t warp_scratch_bytes(uint32_t cache_log2) {
+  return (size_t)kStageBytes + ((size_t)4 << cache_log2) + (size_t)kIdsCap * 4;
+}
+__device__ __forceinline__ WarpScratch make_warp_scratch(unsigned char* mine, uint32_t cache_log2) {
+  WarpScratch ws;
+  ws.stage = reinterpret_cast<uint4*>(mine);
+  ws.cache = reinterpret_cast<uint32_t*>(mine + kStageBytes);
+  ws.cache_shift = 32u - cache_log2;
+  ws.ids = reinterpret_cast<uint32_t*>(mine + kStageBytes + ((size_t)4 << cache_log2));
+  return ws;
+}
 
 template <int R>
 struct BeamRegs {
@@ -178,15 +198,29 @@ struct BeamRegs {
 // Distances of the n (1..32) sketches whose gids are staged in ids[0..n) to the query piece qv:
 // lane i returns the distance of ids[i] (garbage for i >= n).  Lane = (g = lane / 8, s = lane % 8) owns the
 // s-th 16-B piece of rows 4 * j + g, j = 0..7.
-__device__ __forceinline__ uint32_t hamming32(const uint4* __restrict__ sk, const uint32_t* ids, uint32_t n, uint4 qv) {
+__device__ __forceinline__ uint32_t hamming32(const uint4* __restrict__ sk, const uint32_t* ids, uint32_t n, uint4 qv, uint4* stage) {
   const uint32_t lane = threadIdx.x & 31, g = lane >> 3, s = lane & 7u;
+  uint32_t x[8];
+#if HB_GATHER_CPASYNC
+  // every lane copies exactly the 16-B pieces it reads back below, so cp.async.wait_group is the only ordering needed
+  uint4* const mine = stage + g * 8 + s;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (4u * j < n) {
+      const uint4* src = sk + (size_t)ids[min(4u * j + g, n - 1u)] * 8 + s;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(mine + j * 32)), "l"(src) : "memory");
+    }
+  asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+  for (int j = 0; j < 8; ++j) x[j] = (4u * j < n) ? popc_xor4(mine[j * 32], qv) : 0u;
+#else
   uint4 v[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j)
     if (4u * j < n) v[j] = __ldg(sk + (size_t)ids[min(4u * j + g, n - 1u)] * 8 + s);
-  uint32_t x[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) x[j] = (4u * j < n) ? popc_xor4(v[j], qv) : 0u;
+#endif
   // butterfly: after the three rounds lane (g, s) holds the full sum of row 4 * s + g
   const bool b0 = s & 1u, b1 = s & 2u, b2 = s & 4u;
   uint32_t y[4];
@@ -391,7 +425,7 @@ __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint3
         const uint32_t n = min(32u, n_new - g0);
         HB_TICK(t_g0);
         const uint32_t myid = ws.ids[g0 + (lane < n ? lane : 0u)];
-        const uint32_t myd = hamming32(gv.sk, ws.ids + g0, n, qv);  // nsw.rs:164-165
+        const uint32_t myd = hamming32(gv.sk, ws.ids + g0, n, qv, ws.stage);  // nsw.rs:164-165
         if (!sk_done) {
           prefetch_row_sketches(gv.sk, pw0, pw1);
           sk_done = true;

@@ -92,13 +92,7 @@ struct Step {
 
 // ---- kernels -------------------------------------------------------------------------------------
 
-__device__ __forceinline__ WarpScratch warp_scratch(unsigned char* mine) {
-  WarpScratch ws;
-  ws.cache = reinterpret_cast<uint32_t*>(mine);
-  ws.cache_shift = 32u - kBuildCacheLog2;
-  ws.ids = reinterpret_cast<uint32_t*>(mine + ((size_t)4 << kBuildCacheLog2));
-  return ws;
-}
+__device__ __forceinline__ WarpScratch warp_scratch(unsigned char* mine) { return make_warp_scratch(mine, kBuildCacheLog2); }
 
 // ef = 1 descent through graphs g_top .. g_stop + 1 (hnsw.rs:94-108); eps[j] = entry index local to graph g_stop.
 __global__ void __launch_bounds__(kBuildWarps * 32) build_descent_kernel(const BuildCtx c, uint32_t point_first, uint32_t count,
@@ -107,7 +101,7 @@ __global__ void __launch_bounds__(kBuildWarps * 32) build_descent_kernel(const B
   const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const uint32_t j = blockIdx.x * kBuildWarps + wib;
   if (j >= count) return;
-  const size_t per_warp = ((size_t)4 << kBuildCacheLog2) + kIdsCap * 4;
+  const size_t per_warp = warp_scratch_bytes(kBuildCacheLog2);
   const WarpScratch ws = warp_scratch(smem_raw + wib * per_warp);
   const GraphView gv{c.sk, c.adj, c.stride};
   const uint4 qv = __ldg(c.sk + (size_t)(point_first + j) * 8 + (lane & 7u));
@@ -134,10 +128,10 @@ __global__ void __launch_bounds__(kBuildWarps * 32) build_search_select_kernel(c
   const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5, grp = lane >> 3, s = lane & 7u;
   const uint32_t j = blockIdx.x * kBuildWarps + wib;
   if (j >= count) return;
-  const size_t per_warp = ((size_t)4 << kBuildCacheLog2) + kIdsCap * 4 + (size_t)c.m * 128;
+  const size_t per_warp = warp_scratch_bytes(kBuildCacheLog2) + (size_t)c.m * 128;
   unsigned char* mine = smem_raw + wib * per_warp;
   const WarpScratch ws = warp_scratch(mine);
-  uint4* sel_sk = reinterpret_cast<uint4*>(mine + ((size_t)4 << kBuildCacheLog2) + kIdsCap * 4);  // [m][8]
+  uint4* sel_sk = reinterpret_cast<uint4*>(mine + warp_scratch_bytes(kBuildCacheLog2));  // [m][8]
   const GraphView gv{c.sk, c.adj, c.stride};
   const uint32_t self = node_first + j;
   const uint4 qv = __ldg(c.sk + (size_t)self * 8 + s);
@@ -578,8 +572,8 @@ Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& bp, i
   c.stamp = d_stamp.p;
 
   const SelectKernel select_kernel = select_kernel_for(efc);
-  const size_t smem_descent = (size_t)kBuildWarps * (((size_t)4 << kBuildCacheLog2) + kIdsCap * 4);
-  const size_t smem_select = (size_t)kBuildWarps * (((size_t)4 << kBuildCacheLog2) + kIdsCap * 4 + (size_t)m * 128);
+  const size_t smem_descent = (size_t)kBuildWarps * warp_scratch_bytes(kBuildCacheLog2);
+  const size_t smem_select = (size_t)kBuildWarps * (warp_scratch_bytes(kBuildCacheLog2) + (size_t)m * 128);
   const size_t smem_prune = (size_t)(idx->stride - 1) * 128 + kPruneCap * 8 + kPruneCap * 2 + kPruneCap;
   HB_CUDA(cudaFuncSetAttribute(select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_select));
   HB_CUDA(cudaFuncSetAttribute(build_prune_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_prune));

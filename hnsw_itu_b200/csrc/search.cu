@@ -325,18 +325,15 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) hnsw_search_kernel(con
 constexpr uint32_t kFastSpillCap = 64;
 
 #ifndef HB_MIN_BLOCKS
-#define HB_MIN_BLOCKS 6
+#define HB_MIN_BLOCKS 7
 #endif
 template <int R>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS) hnsw_search_fast_kernel(const SearchParams p, uint32_t cache_log2) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const size_t per_warp = ((size_t)4 << cache_log2) + kIdsCap * 4 + kFastSpillCap * 4;
+  const size_t per_warp = warp_scratch_bytes(cache_log2) + kFastSpillCap * 4;
   unsigned char* mine = smem_raw + wib * per_warp;
-  WarpScratch ws;
-  ws.cache = reinterpret_cast<uint32_t*>(mine);
-  ws.cache_shift = 32u - cache_log2;
-  ws.ids = reinterpret_cast<uint32_t*>(mine + ((size_t)4 << cache_log2));
+  const WarpScratch ws = make_warp_scratch(mine, cache_log2);
   uint32_t* const spill = ws.ids + kIdsCap;
   const GraphView gv{p.sk, p.adj, p.stride};
   const uint32_t sub = lane & 7u;
@@ -348,6 +345,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS) hnsw_searc
     if (qi >= p.nq) break;
     const uint32_t q = p.qmap ? p.qmap[qi] : qi;
     const uint4 qv = __ldg(p.queries + (size_t)q * 8 + sub);
+#ifdef HB_DIAG_TIME
+    unsigned long long t_start;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+#endif
     cache_clear(ws);
 
     SearchCounters c;
@@ -380,7 +381,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS) hnsw_searc
       p.found[q] = nres;
       p.qstatus[q] = status;
       if (status) atomicOr(p.ctl + 1, 1u);
+#ifdef HB_DIAG_TIME
+      // diagnostics build: (start ns, end ns, warp slot, X) instead of the work counters
+      unsigned long long t_end;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+      if (p.counters) p.counters[q] = make_uint4((uint32_t)t_start, (uint32_t)t_end, blockIdx.x * kWarpsPerBlock + wib, c.X);
+#else
       if (p.counters) p.counters[q] = make_uint4(c.X, c.E, c.V, c.A);
+#endif
     }
     __syncwarp();
   }
@@ -501,9 +509,9 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   static const bool force_large = std::getenv("HB_FORCE_LARGE") != nullptr;
   if (ef <= 256 && !force_large) {
     static const int env_cache = std::getenv("HB_CACHE_LOG2") ? std::atoi(std::getenv("HB_CACHE_LOG2")) : 0;
-    uint32_t cache_log2 = env_cache >= 5 && env_cache <= 13 ? (uint32_t)env_cache : 10u;
+    uint32_t cache_log2 = env_cache >= 5 && env_cache <= 13 ? (uint32_t)env_cache : 9u;
     const FastLaunch fl = fast_kernel_for(ef);
-    const size_t fsmem = (size_t)kWarpsPerBlock * (((size_t)4 << cache_log2) + kIdsCap * 4 + kFastSpillCap * 4);
+    const size_t fsmem = (size_t)kWarpsPerBlock * (warp_scratch_bytes(cache_log2) + kFastSpillCap * 4);
     HB_CUDA(cudaFuncSetAttribute(fl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
     int fbps = 0;
     HB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fbps, fl.kernel, kWarpsPerBlock * 32, fsmem));
