@@ -92,6 +92,8 @@ def lib() -> C.CDLL:
     L.hb_kernel_launches.restype = C.c_uint64
     L.hb_ground_truth.argtypes = [_u64p, C.c_uint64, _u64p, C.c_uint64, C.c_uint32, C.c_int, _u64p, _u64p]
     L.hb_ground_truth_device.argtypes = [vp, C.c_uint64, C.c_uint64, vp, C.c_uint64, C.c_uint32, vp, vp]
+    L.hb_ground_truth_algo.argtypes = [_u64p, C.c_uint64, _u64p, C.c_uint64, C.c_uint32, C.c_int, C.c_int, _u64p, _u64p]
+    L.hb_ground_truth_device_algo.argtypes = [vp, C.c_uint64, C.c_uint64, vp, C.c_uint64, C.c_uint32, C.c_int, vp, vp]
     L.hb_topk_merge_device.argtypes = [vp, C.c_uint32, C.c_uint64, C.c_uint32, vp, vp]
     L.hb_unpack_device.argtypes = [vp, C.c_uint64, vp, vp, vp]
     L.hb_pack_device.argtypes = [vp, vp, vp, C.c_uint64, C.c_uint32, C.c_uint64, vp, vp]

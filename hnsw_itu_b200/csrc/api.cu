@@ -315,13 +315,18 @@ int hb_search(const hb_index* h, const uint64_t* query, uint32_t k, uint32_t ef,
   return hb_knns(h, query, 1, k, ef, flags, keys, dists, found, nullptr);
 }
 
-int hb_ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
-                           void* d_packed, void* stream) {
+int hb_ground_truth_device_algo(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
+                                int algo, void* d_packed, void* stream) {
   return guarded([&] {
     HB_REQUIRE(nq == 0 || (d_queries && d_packed), HB_ERR_INVALID, "null device buffer");
     HB_REQUIRE(n == 0 || d_data, HB_ERR_INVALID, "null device buffer");
-    ground_truth_device(d_data, n, key_offset, d_queries, nq, k, d_packed, static_cast<cudaStream_t>(stream));
+    ground_truth_device(d_data, n, key_offset, d_queries, nq, k, d_packed, static_cast<cudaStream_t>(stream), algo);
   });
+}
+
+int hb_ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
+                           void* d_packed, void* stream) {
+  return hb_ground_truth_device_algo(d_data, n, key_offset, d_queries, nq, k, HB_GT_AUTO, d_packed, stream);
 }
 
 int hb_topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_packed_out, void* stream) {
@@ -349,6 +354,11 @@ int hb_pack_device(const void* d_keys, const void* d_dists, const void* d_found,
 
 int hb_ground_truth(const uint64_t* data, uint64_t n, const uint64_t* queries, uint64_t nq, uint32_t k, int device, uint64_t* keys,
                     uint64_t* dists) {
+  return hb_ground_truth_algo(data, n, queries, nq, k, device, HB_GT_AUTO, keys, dists);
+}
+
+int hb_ground_truth_algo(const uint64_t* data, uint64_t n, const uint64_t* queries, uint64_t nq, uint32_t k, int device, int algo,
+                         uint64_t* keys, uint64_t* dists) {
   return guarded([&] {
     HB_REQUIRE(nq == 0 || (queries && keys && dists), HB_ERR_INVALID, "null host buffer");
     HB_REQUIRE(n == 0 || data, HB_ERR_INVALID, "null host buffer");
@@ -357,7 +367,7 @@ int hb_ground_truth(const uint64_t* data, uint64_t n, const uint64_t* queries, u
     DevMem<uint64_t> dd(n * 16), dq(nq * 16), dp(nq * k), dk(nq * k), ds(nq * k);
     if (n) HB_CUDA(cudaMemcpy(dd.p, data, n * 128, cudaMemcpyHostToDevice));
     HB_CUDA(cudaMemcpy(dq.p, queries, nq * 128, cudaMemcpyHostToDevice));
-    ground_truth_device(dd.p, n, 0, dq.p, nq, k, dp.p, nullptr);
+    ground_truth_device(dd.p, n, 0, dq.p, nq, k, dp.p, nullptr, algo);
     unpack_device(dp.p, nq * k, dk.p, ds.p, nullptr);
     HB_CUDA(cudaMemcpy(keys, dk.p, nq * k * 8, cudaMemcpyDeviceToHost));
     HB_CUDA(cudaMemcpy(dists, ds.p, nq * k * 8, cudaMemcpyDeviceToHost));

@@ -185,7 +185,18 @@ void unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists
 }
 
 void ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
-                         void* d_packed, cudaStream_t stream) {
+                         void* d_packed, cudaStream_t stream, int algo) {
+  HB_REQUIRE(algo == HB_GT_AUTO || algo == HB_GT_SCAN || algo == HB_GT_MMA, HB_ERR_INVALID, "unknown ground-truth algorithm");
+  if (algo == HB_GT_AUTO)
+    algo = (nq >= 32 && n >= 4096 && ground_truth_mma_supported(d_data, d_queries, n, nq, k)) ? HB_GT_MMA : HB_GT_SCAN;
+  if (algo == HB_GT_MMA)
+    ground_truth_mma_device(d_data, n, key_offset, d_queries, nq, k, d_packed, stream);
+  else
+    ground_truth_scan_device(d_data, n, key_offset, d_queries, nq, k, d_packed, stream);
+}
+
+void ground_truth_scan_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
+                              void* d_packed, cudaStream_t stream) {
   HB_REQUIRE(k >= 1 && k <= 1024, HB_ERR_UNSUPPORTED, "ground truth supports 1 <= k <= 1024");
   HB_REQUIRE(key_offset + n <= 0xFFFFFFFFull, HB_ERR_UNSUPPORTED, "keys must stay below 2^32");
   HB_REQUIRE(nq <= 0xFFFFFFF0ull, HB_ERR_UNSUPPORTED, "too many queries in one call");

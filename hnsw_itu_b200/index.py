@@ -196,13 +196,17 @@ def index_from_parts(algo: str, graphs: list[dict], ep: int | None, device: int 
     return Index(h.value)
 
 
-def ground_truth(data, queries, k: int, device: int = 0):
+GT_ALGOS = {"auto": 0, "scan": 1, "mma": 2}  # hb_gt_algo
+
+
+def ground_truth(data, queries, k: int, device: int = 0, algo: str = "auto"):
     """CLI `ground-truth` (cli/src/main.rs:715-754): exact k smallest (distance, key) per query,
-    ascending; returns 0-based keys (nq,k) u64 and dists (nq,k) u64."""
+    ascending; returns 0-based keys (nq,k) u64 and dists (nq,k) u64.  `algo`: "auto", "scan" (XOR+POPC) or
+    "mma" (tcgen05 int8 GEMM) -- identical results."""
     d, q = _sketches(data) if len(data) else np.zeros((0, 16), dtype=np.uint64), _sketches(queries)
     keys = np.zeros((len(q), k), dtype=np.uint64)
     dists = np.zeros((len(q), k), dtype=np.uint64)
-    check(_lib.lib().hb_ground_truth(_p(d), len(d), _p(q), len(q), k, device, _p(keys), _p(dists)))
+    check(_lib.lib().hb_ground_truth_algo(_p(d), len(d), _p(q), len(q), k, device, GT_ALGOS[algo], _p(keys), _p(dists)))
     return keys, dists
 
 

@@ -154,12 +154,13 @@ def test_ground_truth_parity(hb, oracle):
         p = orc.SynthParams(latent_dim=8, n_clusters=16, distinct_planes=dp)
         data = oracle.synth(n, 61, p)
         q = oracle.synth(nq, 62, p)
-        gk, gd = hb.ground_truth(data, q, k)
         ok, od = oracle.ground_truth(data, q, k)
         m = min(n, k)
-        assert np.array_equal(gk[:, :m], ok[:, :m]) and np.array_equal(gd[:, :m], od[:, :m]), (dp, n, nq, k)
-        if n < k:
-            assert (gk[:, m:] == np.uint64(2**64 - 1)).all()
+        for algo in ("auto", "scan", "mma"):
+            gk, gd = hb.ground_truth(data, q, k, algo=algo)
+            assert np.array_equal(gk[:, :m], ok[:, :m]) and np.array_equal(gd[:, :m], od[:, :m]), (dp, n, nq, k, algo)
+            if n < k:
+                assert (gk[:, m:] == np.uint64(2**64 - 1)).all()
     exp = np.load(os.path.join(G, "tiny_expected.npz"))
     data = oracle.load_idx(os.path.join(G, "tiny_hnsw.idx")).graph(0)["sketches"]
     gk, gd = hb.ground_truth(data, _queries(), 10)
@@ -169,6 +170,58 @@ def test_ground_truth_parity(hb, oracle):
     bk, bd, bfnd = bf.knns_arrays(_queries(), 10, 3)
     ok, od = oracle.ground_truth(data[:100], _queries(), 10)
     assert np.array_equal(bk, ok) and np.array_equal(bd, od) and (bfnd == 10).all()
+
+
+@pytest.mark.parametrize("dp,n,nq,k", [
+    (1024, 20000, 300, 10),   # several query tiles (last one ragged), many data tiles
+    (16, 9001, 129, 100),     # distances in multiples of 64: ties everywhere, k = 100, ragged last data tile
+    (1024, 255, 1, 10),       # less than one data tile, one query
+    (64, 70000, 128, 1),      # k = 1; more items than SMs' worth of chunks
+    (1024, 513, 257, 1024),   # k > rows in most chunks, k at the supported maximum
+])
+def test_ground_truth_tcgen05_vs_oracle(hb, oracle, dp, n, nq, k):
+    """The tcgen05 int8-GEMM formulation (gt_tcgen05.cu) against Bruteforce::search + sort restated by the oracle,
+    and against the XOR+POPC scan kernel: ids and distances identical, including the (distance, key) tie order."""
+    from oracle import oracle as orc
+    p = orc.SynthParams(latent_dim=8, n_clusters=16, distinct_planes=dp)
+    data = oracle.synth(n, 161, p)
+    q = oracle.synth(nq, 162, p)
+    q[0] = data[n // 2]            # a query that is a member: distance 0
+    if nq > 1:
+        q[-1] = ~data[n - 1]       # and the complement of the last row: distance 1024 to it
+    mk, md = hb.ground_truth(data, q, k, algo="mma")
+    sk, sd = hb.ground_truth(data, q, k, algo="scan")
+    assert np.array_equal(mk, sk) and np.array_equal(md, sd)
+    ok, od = oracle.ground_truth(data, q, k)
+    m = min(n, k)
+    assert np.array_equal(mk[:, :m], ok[:, :m]) and np.array_equal(md[:, :m], od[:, :m])
+    assert md[0, 0] == 0 and mk[0, 0] <= n // 2
+
+
+def test_ground_truth_tcgen05_all_bit_positions(hb):
+    """Every one of the 1024 bit positions contributes exactly 1 to the distance (the operand scaling/permutation
+    of the int8 expansion is position dependent): rows = one-hot sketches against the zero query and its complement."""
+    data = np.zeros((1024 + 300, 16), dtype=np.uint64)
+    for b in range(1024):
+        data[b, b // 64] = np.uint64(1) << np.uint64(b % 64)
+    for r in range(300):   # r low bits set
+        bits = r + 2
+        for w in range(16):
+            nb = min(64, max(0, bits - 64 * w))
+            data[1024 + r, w] = np.uint64((1 << nb) - 1) if nb < 64 else np.uint64(2**64 - 1)
+    q = np.zeros((40, 16), dtype=np.uint64)
+    q[1] = ~q[1]
+    for i in range(2, 40):
+        q[i] = data[(i * 37) % 1024] | data[(i * 91 + 5) % 1024]
+    mk, md = hb.ground_truth(data, q, 50, algo="mma")
+    sk, sd = hb.ground_truth(data, q, 50, algo="scan")
+    assert np.array_equal(mk, sk) and np.array_equal(md, sd)
+    assert (md[0, :50] == 1).all() and np.array_equal(mk[0, :50], np.arange(50, dtype=np.uint64))
+    x = data[:, None, :] ^ q[None, :3, :]
+    ref = np.unpackbits(x.view(np.uint8), axis=-1).sum(-1).astype(np.uint64)   # (n, 3)
+    for j in range(3):
+        order = np.lexsort((np.arange(len(data)), ref[:, j]))[:50]
+        assert np.array_equal(mk[j], order.astype(np.uint64)) and np.array_equal(md[j], ref[order, j])
 
 
 def test_sharded_ground_truth_merge(hb, oracle):
