@@ -86,6 +86,17 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da, uint64_t d
       "l"(da), "l"(db), "r"(kIdesc), "r"(accumulate)
       : "memory");
 }
+// one lane of the (converged) warp; ptxas knows the guarded region is single-threaded, so UTCIMMA needs no lane loop
+__device__ __forceinline__ uint32_t elect_one_sync() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, %1;\n\t"
+      "@px mov.s32 %0, 1;\n\t}"
+      : "+r"(pred)
+      : "r"(0xFFFFFFFFu));
+  return pred;
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -102,6 +113,25 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
       : "r"(taddr)                                                                                                      \
       : "memory")
 
+#ifdef HB_GT_DIAG
+// per-CTA phase clocks (diagnostic build only, tools/gt_diag.py): [0] kernel cycles, [1] MMA warp waiting for a free
+// accumulator, [2] MMA warp waiting for a full stage, [3] expansion warp 0 waiting for an empty stage, [4] its fences,
+// [5] epilogue warp 0 waiting for a full accumulator, [6] its inserts, [7] tiles, [8] expansion waiting for A free
+__device__ long long g_gt_diag[256 * 16];
+// trace of CTA 0, tiles [kTr0, kTr0+32): at g_gt_diag[2400 + 32*(tile-kTr0) + slot]
+//   slot 0 MMA passes acc-free wait, 1 MMA issued last stage, 2+w epilogue warp w sees acc full, 6+w warp w releases acc,
+//   10+kb expansion warp 0 arrives stage kb, 18+kb MMA passes full wait of stage kb
+constexpr uint32_t kTr0 = 3000;
+#define HB_TRACE(tile, slot) \
+  do { if (blockIdx.x == 0 && (tile) >= kTr0 && (tile) < kTr0 + 32 && (threadIdx.x & 31) == 0) g_gt_diag[2400 + 32 * ((tile) - kTr0) + (slot)] = clock64(); } while (0)
+#define HB_DIAG_T0() const long long dg_t0 = clock64()
+#define HB_DIAG_ADD(var) var += clock64() - dg_t0
+#else
+#define HB_TRACE(tile, slot)
+#define HB_DIAG_T0()
+#define HB_DIAG_ADD(var)
+#endif
+
 struct GtParams {
   const uint64_t* data;     // n rows x 16 u64
   const uint64_t* queries;  // nq rows x 16 u64
@@ -112,24 +142,35 @@ struct GtParams {
   uint32_t n_qtiles, n_chunks, tiles_per_chunk, n_tiles;
 };
 
-// single-thread insert into the thread's ascending list; returns the new accumulator threshold
+// k > 16: single-thread insert into the thread's ascending list in global memory (binary search for the slot, then the
+// tail moves up in batches of independent loads); returns the new accumulator threshold
 __device__ __noinline__ int gt_insert(uint64_t* list, uint32_t k, int popq, int acc, uint32_t key, int T, uint32_t* gthr) {
   const uint64_t v = ((uint64_t)(uint32_t)(popq - (acc >> 6)) << 32) | key;
   if (v >= list[k - 1]) return T;
-  uint32_t i = k - 1;
-  while (i > 0) {
-    const uint64_t e = list[i - 1];
-    if (e <= v) break;
-    list[i] = e;
-    --i;
+  uint32_t lo = 0, hi = k - 1;  // first index whose element exceeds v is in [lo, hi]
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (list[mid] > v) hi = mid;
+    else lo = mid + 1;
   }
-  list[i] = v;
+  uint32_t i = k - 1;
+  while (i >= lo + 8) {
+    uint64_t e[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) e[j] = list[i - 1 - j];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) list[i - j] = e[j];
+    i -= 8;
+  }
+  for (; i > lo; --i) list[i] = list[i - 1];
+  list[lo] = v;
   const uint64_t last = list[k - 1];
   if (last == kNone) return INT_MIN;
   atomicMin(gthr, (uint32_t)(last >> 32));
   return 64 * (popq - (int)(uint32_t)(last >> 32));
 }
 
+template <bool kRegList>
 __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -170,12 +211,16 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
     // ===================== epilogue: thread = one query row of the accumulator =====================
     const uint32_t row = warp * 32 + lane;
     uint32_t tcount = 0;
+    [[maybe_unused]] long long dg_tfull = 0, dg_ins = 0;
     for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
       const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
       const uint32_t q = qtile * kTileM + row;
       const bool live = q < p.nq;
       uint64_t* list = p.partial + ((size_t)chunk * p.nq + (live ? q : 0)) * p.k;
+      // k <= 16: the row's ascending list lives in registers, right-aligned (rl[16-k..15]; the slots before it hold 0,
+      // which no element displaces), so the k-th best is always rl[15] and every index is static
+      uint64_t rl[kRegList ? 16 : 1];
       int popq = 0;
       if (live) {
         const uint4* qp = reinterpret_cast<const uint4*>(p.queries + (size_t)q * 16);
@@ -184,7 +229,12 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
           const uint4 w = __ldg(qp + j);
           popq += __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w);
         }
-        for (uint32_t i = 0; i < p.k; ++i) list[i] = kNone;
+        if (!kRegList)
+          for (uint32_t i = 0; i < p.k; ++i) list[i] = kNone;
+      }
+      if (kRegList) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) rl[i] = ((uint32_t)i + p.k < 16u) ? 0ull : kNone;
       }
       // The accumulator must exceed T to beat this item's current k-th best (strict: keys ascend inside an item), and
       // must exceed Tg to be at most the best k-th distance any item has reached for this query (ties kept: the
@@ -195,7 +245,12 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
       for (uint32_t t = t0; t < t1; ++t, ++tcount) {
         const uint32_t acc = tcount & 1, use = tcount >> 1;
         const uint32_t g_now = *reinterpret_cast<volatile uint32_t*>(gq);
-        mbar_wait(bTFull + 8 * acc, use & 1);
+        {
+          HB_DIAG_T0();
+          mbar_wait(bTFull + 8 * acc, use & 1);
+          HB_DIAG_ADD(dg_tfull);
+        }
+        HB_TRACE(tcount, 2 + warp);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int Tg = (g_now == 0xFFFFFFFFu) ? INT_MIN : 64 * (popq - (int)g_now) - 64;
         int Te = max(T, Tg);
@@ -203,33 +258,89 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
         const uint64_t tile_row0 = (uint64_t)t * kTileN;
 #pragma unroll 1
         for (int g = 0; g < kTileN / 64; ++g) {
-          int v[64];
-          HB_TMEM_LD32(v, taddr + g * 64);
-          HB_TMEM_LD32((v + 32), taddr + g * 64 + 32);
-          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-          int mx = v[0];
+          uint32_t h0 = 0, h1 = 0;
+          bool hit;
+          {
+            int v[64];
+            HB_TMEM_LD32(v, taddr + g * 64);
+            HB_TMEM_LD32((v + 32), taddr + g * 64 + 32);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            int mx = v[0];
 #pragma unroll
-          for (int c = 1; c < 64; c += 1) mx = max(mx, v[c]);
-          if (mx > Te) {
-            const uint64_t r0 = tile_row0 + (uint64_t)g * 64;
+            for (int c = 1; c < 64; c += 1) mx = max(mx, v[c]);
+            hit = __any_sync(0xFFFFFFFFu, mx > Te);
+            if (hit) {  // warp-uniform: which columns pass for which lane
 #pragma unroll
-            for (int c = 0; c < 64; ++c) {
-              if (v[c] > Te && r0 + c < row_end) {
-                T = gt_insert(list, p.k, popq, v[c], (uint32_t)(p.key_offset + r0 + c), T, gq);
-                Te = max(T, Tg);
+              for (int c = 0; c < 32; ++c) {
+                h0 |= (uint32_t)(v[c] > Te) << c;
+                h1 |= (uint32_t)(v[32 + c] > Te) << c;
               }
             }
+          }
+          if (hit) {
+            // Rare path, kept warp-uniform: for every column some lane wants, each lane re-reads its own value of that
+            // column from TMEM (the accumulator is still ours) and the lanes that pass run one copy of the insert.
+            HB_DIAG_T0();
+            const uint64_t r0 = tile_row0 + (uint64_t)g * 64;
+            const uint32_t nvalid = (uint32_t)min((uint64_t)64, row_end > r0 ? row_end - r0 : 0);
+            uint64_t m = (uint64_t)__reduce_or_sync(0xFFFFFFFFu, h0) | ((uint64_t)__reduce_or_sync(0xFFFFFFFFu, h1) << 32);
+            if (nvalid < 64) m &= (1ull << nvalid) - 1ull;
+            {
+              while (m) {
+                const uint32_t col = (uint32_t)__ffsll((long long)m) - 1u;
+                m &= m - 1;
+                int x;
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(x) : "r"(taddr + g * 64 + col) : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (x > Te) {
+                  const uint32_t key = (uint32_t)(p.key_offset + r0 + col);
+                  if (kRegList) {
+                    const uint64_t e = ((uint64_t)(uint32_t)(popq - (x >> 6)) << 32) | key;
+#pragma unroll
+                    for (int i = 15; i > 0; --i) {
+                      if (rl[i - 1] > e) rl[i] = rl[i - 1];
+                      else if (rl[i] > e) rl[i] = e;
+                    }
+                    if (rl[0] > e) rl[0] = e;
+                    const uint64_t last = rl[15];
+                    if (last != kNone) {
+                      atomicMin(gq, (uint32_t)(last >> 32));
+                      T = 64 * (popq - (int)(uint32_t)(last >> 32));
+                    }
+                  } else {
+                    T = gt_insert(list, p.k, popq, x, key, T, gq);
+                  }
+                  Te = max(T, Tg);
+                }
+              }
+            }
+            HB_DIAG_ADD(dg_ins);
           }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         mbar_arrive(bTEmpty + 8 * acc);
+        HB_TRACE(tcount, 6 + warp);
+      }
+      if (kRegList && live) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if ((uint32_t)i + p.k >= 16u) list[(uint32_t)i + p.k - 16u] = rl[i];
       }
     }
+#ifdef HB_GT_DIAG
+    if (warp == 0 && lane == 0) {
+      g_gt_diag[blockIdx.x * 16 + 5] = dg_tfull;
+      g_gt_diag[blockIdx.x * 16 + 6] = dg_ins;
+      g_gt_diag[blockIdx.x * 16 + 7] = tcount;
+    }
+#endif
   } else if (warp < kEpiWarps + kExpWarps) {
     // ===================== expansion: packed bits -> int8 operands in shared memory =====================
     const uint32_t ew = warp - kEpiWarps;
     const uint32_t et = ew * 32 + lane;  // 0..255: row of the data tile
-    uint32_t fill = 0, it = 0;
+    uint32_t stage = 0, sphase = 0, it = 0;
+    [[maybe_unused]] long long dg_empty = 0, dg_fence = 0, dg_afree = 0;
+    [[maybe_unused]] uint32_t xt = 0;
     for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
@@ -250,7 +361,11 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
         }
       }
       // ---- A: the query tile, +-(64 >> s) per bit (s = 7 shares scale 1 with s = 6's data scale 64) ----
-      mbar_wait(bAFree, (it & 1) ^ 1);
+      {
+        HB_DIAG_T0();
+        mbar_wait(bAFree, (it & 1) ^ 1);
+        HB_DIAG_ADD(dg_afree);
+      }
       {
         const uint32_t arow = et >> 1, kb0 = (et & 1) * 4;
         const uint32_t q = qtile * kTileM + arow;
@@ -282,6 +397,9 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
         if (lane == 0) mbar_arrive(bAFull);
       }
       // ---- B: data tiles ----
+      // The next tile's row is fetched at the top of the tile (four 256-bit loads).  Every stage's proxy fence is a
+      // MEMBAR that waits for outstanding loads, so the load latency is exposed once per tile, overlapped with the
+      // wait for the first free stage.
       for (uint32_t t = t0; t < t1; ++t) {
         const uint64_t rn = (uint64_t)(t + 1) * kTileN + et;
         if (t + 1 < t1 && rn < p.n) {
@@ -296,9 +414,12 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
           for (int j = 0; j < 16; ++j) nxt[j] = 0;
         }
 #pragma unroll
-        for (int kb = 0; kb < kKBlocks; ++kb, ++fill) {
-          const uint32_t stage = fill % kStages, use = fill / kStages;
-          mbar_wait(bEmpty + 8 * stage, (use & 1) ^ 1);
+        for (int kb = 0; kb < kKBlocks; ++kb) {
+          {
+            HB_DIAG_T0();
+            mbar_wait(bEmpty + 8 * stage, sphase ^ 1);
+            HB_DIAG_ADD(dg_empty);
+          }
           const uint32_t w[4] = {(uint32_t)cur[2 * kb], (uint32_t)(cur[2 * kb] >> 32), (uint32_t)cur[2 * kb + 1],
                                  (uint32_t)(cur[2 * kb + 1] >> 32)};
           const uint32_t rowaddr = sB + stage * kStageBytes + et * 128;
@@ -314,33 +435,66 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
                          "r"(o[2]), "r"(o[3])
                          : "memory");
           }
-          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-          __syncwarp();
+          {
+            HB_DIAG_T0();
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            HB_DIAG_ADD(dg_fence);
+          }
           if (lane == 0) mbar_arrive(bFull + 8 * stage);
+          if (ew == 0) HB_TRACE(xt, 10 + kb);
+          if (++stage == kStages) {
+            stage = 0;
+            sphase ^= 1;
+          }
         }
 #pragma unroll
         for (int j = 0; j < 16; ++j) cur[j] = nxt[j];
+#ifdef HB_GT_DIAG
+        ++xt;
+#endif
       }
     }
+#ifdef HB_GT_DIAG
+    if (ew == 0 && lane == 0) {
+      g_gt_diag[blockIdx.x * 16 + 3] = dg_empty;
+      g_gt_diag[blockIdx.x * 16 + 4] = dg_fence;
+      g_gt_diag[blockIdx.x * 16 + 8] = dg_afree;
+    }
+#endif
   } else {
-    // ===================== MMA issue: one thread =====================
-    uint32_t cons = 0, tcount = 0, it = 0;
+    // ===================== MMA issue: one elected thread =====================
+    uint32_t stage = 0, sphase = 0, tcount = 0, it = 0;
+    [[maybe_unused]] long long dg_tempty = 0, dg_full = 0;
+    [[maybe_unused]] const long long dg_start = clock64();
+    const uint64_t da0 = umma_desc(sA), db0 = umma_desc(sB);
     for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const uint32_t chunk = item / p.n_qtiles;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
       mbar_wait(bAFull, it & 1);
       for (uint32_t t = t0; t < t1; ++t, ++tcount) {
         const uint32_t acc = tcount & 1, ause = tcount >> 1;
-        mbar_wait(bTEmpty + 8 * acc, (ause & 1) ^ 1);
-        for (int kb = 0; kb < kKBlocks; ++kb, ++cons) {
-          const uint32_t stage = cons % kStages, use = cons / kStages;
-          mbar_wait(bFull + 8 * stage, use & 1);
+        {
+          HB_DIAG_T0();
+          mbar_wait(bTEmpty + 8 * acc, (ause & 1) ^ 1);
+          HB_DIAG_ADD(dg_tempty);
+        }
+        HB_TRACE(tcount, 0);
+        const uint32_t tmem_d = tmem + acc * kTileN;
+#pragma unroll
+        for (int kb = 0; kb < kKBlocks; ++kb) {
+          {
+            HB_DIAG_T0();
+            mbar_wait(bFull + 8 * stage, sphase);
+            HB_DIAG_ADD(dg_full);
+          }
+          HB_TRACE(tcount, 18 + kb);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          if (lane == 0) {
-            const uint64_t da = umma_desc(sA + kb * kAKBlockBytes), db = umma_desc(sB + stage * kStageBytes);
+          if (elect_one_sync()) {
+            const uint64_t da = da0 + (uint64_t)(kb * (kAKBlockBytes >> 4)), db = db0 + (uint64_t)(stage * (kStageBytes >> 4));
 #pragma unroll
             for (int j = 0; j < 4; ++j)  // K = 32 int8 per instruction: +32 B inside the swizzle atom = +2 in the encoded address
-              umma_i8(tmem + acc * kTileN, da + 2 * j, db + 2 * j, (kb | j) != 0);
+              umma_i8(tmem_d, da + 2 * j, db + 2 * j, (kb | j) != 0);
             umma_commit(bEmpty + 8 * stage);
             if (kb == kKBlocks - 1) {
               umma_commit(bTFull + 8 * acc);
@@ -348,9 +502,21 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
             }
           }
           __syncwarp();
+          if (kb == kKBlocks - 1) HB_TRACE(tcount, 1);
+          if (++stage == kStages) {
+            stage = 0;
+            sphase ^= 1;
+          }
         }
       }
     }
+#ifdef HB_GT_DIAG
+    if (lane == 0) {
+      g_gt_diag[blockIdx.x * 16 + 0] = clock64() - dg_start;
+      g_gt_diag[blockIdx.x * 16 + 1] = dg_tempty;
+      g_gt_diag[blockIdx.x * 16 + 2] = dg_full;
+    }
+#endif
   }
 
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -362,6 +528,12 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
 }
 
 }  // namespace
+
+#ifdef HB_GT_DIAG
+extern "C" int hb_debug_gt_diag(long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, g_gt_diag, sizeof(long long) * 256 * 16);
+}
+#endif
 
 bool ground_truth_mma_supported(const void* d_data, const void* d_queries, uint64_t n, uint64_t nq, uint32_t k) {
   return n >= 1 && nq >= 1 && k >= 1 && k <= 1024 && (reinterpret_cast<uintptr_t>(d_data) & 31) == 0 &&
@@ -395,8 +567,10 @@ void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset
     const uint32_t chunks = (p.n_tiles + tpc - 1) / tpc;
     const uint64_t items = (uint64_t)chunks * p.n_qtiles;
     const uint64_t waves = (items + sms - 1) / sms;
-    // cost model: waves x (tiles per chunk + fixed per-item overhead of ~2 tiles)
-    const double cost = (double)waves * (tpc + 2.0);
+    // cost model: waves x (tiles per chunk + per-item overhead: writing the query tile and refilling the item's lists,
+    // in tile times -- register lists (k <= 16) refill in ~25, lists in global memory in ~4 per entry)
+    const double overhead = 2.0 + (k <= 16 ? 25.0 : 4.0 * k);
+    const double cost = (double)waves * (tpc + overhead);
     const double eff = ((double)p.n_tiles * p.n_qtiles / sms) / cost;
     if (eff > best_eff + 1e-9) {
       best_eff = eff;
@@ -413,9 +587,15 @@ void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset
   p.partial = partial;
   p.gthr = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(partial) + list_bytes);
   HB_CUDA(cudaMemsetAsync(p.gthr, 0xFF, nq * 4, stream));
-  HB_CUDA(cudaFuncSetAttribute(gt_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
   const uint32_t n_items = p.n_qtiles * p.n_chunks;
-  gt_mma_kernel<<<std::min<uint32_t>(n_items, (uint32_t)sms), kThreads, kSmemBytes, stream>>>(p);
+  const uint32_t grid = std::min<uint32_t>(n_items, (uint32_t)sms);
+  if (k <= 16) {
+    HB_CUDA(cudaFuncSetAttribute(gt_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    gt_mma_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(p);
+  } else {
+    HB_CUDA(cudaFuncSetAttribute(gt_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    gt_mma_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(p);
+  }
   count_launches();
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) {
