@@ -4,7 +4,10 @@ rep = sys.argv[1]; top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
-hdr = rows[hi]; body = [r for r in rows[hi + 1:] if len(r) == len(hdr)]
+hdr = rows[hi]; body = []
+for r in rows[hi + 1:]:   # first kernel of the report only
+    if r and r[0] in ("Address", "Kernel Name"): break
+    if len(r) == len(hdr): body.append(r)
 c = {h: i for i, h in enumerate(hdr)}
 stall_cols = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
 tot = sum(int(r[c["# Samples"]] or 0) for r in body)
