@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(kBuildWarps * 32) build_descent_kernel(const B
   uint32_t status = 0;
   BeamRegs<1> b;
   for (int g = g_top; g > g_stop; --g) {
-    beam_search<1>(gv, qv, 1u, cur, ws, c.spill + (size_t)j * c.spill_cap, c.spill_cap, b, sc, status);
+    beam_search(gv, qv, 1u, cur, ws, c.spill + (size_t)j * c.spill_cap, c.spill_cap, b, sc, status);
     cur = __ldg(c.down + (bm_key(b.at(0)) - c.n_base));
   }
   if (lane == 0) {
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(kBuildWarps * 32) build_search_select_kernel(c
   SearchCounters sc;
   uint32_t status = 0;
   BeamRegs<R> b;
-  beam_search<R>(gv, qv, c.efc, c.gbase[g] + c.eps[j], ws, c.spill + (size_t)j * c.spill_cap, c.spill_cap, b, sc, status);
+  beam_search(gv, qv, c.efc, c.gbase[g] + c.eps[j], ws, c.spill + (size_t)j * c.spill_cap, c.spill_cap, b, sc, status);
 
   // select_neighbors (nsw.rs:12-33): ascending (distance, key); keep e iff dist(e, r) > dist(e, q) for every kept r
   uint32_t nsel = 0;
