@@ -77,6 +77,8 @@ def lib() -> C.CDLL:
                                       C.POINTER(vp), C.c_int, C.c_int64, C.c_int, C.c_int, C.POINTER(vp)]
     L.hb_index_save_idx.argtypes = [vp, C.c_char_p]
     L.hb_index_set_attrs.argtypes = [vp, C.c_double, C.c_char_p]
+    L.hb_index_get_attrs.argtypes = [vp, C.POINTER(C.c_int), _u64p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_char_p,
+                                     C.c_uint64, C.c_char_p, C.c_uint64]
     L.hb_index_free.argtypes = [vp]
     L.hb_index_free.restype = None
     L.hb_index_size.argtypes = [vp]

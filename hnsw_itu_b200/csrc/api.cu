@@ -149,6 +149,25 @@ int hb_index_save_idx(const hb_index* h, const char* path) {
   });
 }
 
+int hb_index_get_attrs(const hb_index* h, int* format_size, uint64_t* size, double* buildtime, double* querytime, char* data,
+                       uint64_t data_cap, char* params, uint64_t params_cap) {
+  return guarded([&] {
+    Index* idx = as_index(h);
+    if (format_size) *format_size = idx->attrs.format_size ? 1 : 0;
+    if (size) *size = idx->attrs.size ? idx->attrs.size : idx->n_base;
+    if (buildtime) *buildtime = idx->attrs.buildtime;
+    if (querytime) *querytime = idx->attrs.querytime;
+    auto copy = [](const std::string& s, char* dst, uint64_t cap) {
+      if (!dst || cap == 0) return;
+      const size_t n = std::min<size_t>(s.size(), (size_t)cap - 1);
+      std::memcpy(dst, s.data(), n);
+      dst[n] = 0;
+    };
+    copy(idx->attrs.data, data, data_cap);
+    copy(idx->attrs.params, params, params_cap);
+  });
+}
+
 int hb_index_set_attrs(hb_index* h, double buildtime, const char* params) {
   return guarded([&] {
     Index* idx = as_index(h);

@@ -107,6 +107,10 @@ int hb_index_from_parts(int algo, uint32_t n_graphs, const uint64_t* n_nodes, co
 int hb_index_save_idx(const hb_index* idx, const char* path);
 /* ResultAttrs carried by the .idx (main.rs:311-320); params is "index=(efc=..,m=..,M=..)" */
 int hb_index_set_attrs(hb_index* idx, double buildtime, const char* params);
+/* ResultAttrs as loaded / set (main.rs:311-320): what write_result copies into the result file (main.rs:287-306).
+ * data/params are copied into caller buffers (NUL-terminated, truncated to cap); any pointer may be NULL. */
+int hb_index_get_attrs(const hb_index* idx, int* format_size, uint64_t* size, double* buildtime, double* querytime,
+                       char* data, uint64_t data_cap, char* params, uint64_t params_cap);
 void hb_index_free(hb_index* idx);
 uint64_t hb_index_size(const hb_index* idx); /* Index::size (src/index/mod.rs:22) */
 int hb_index_get_info(const hb_index* idx, hb_index_info* info);
