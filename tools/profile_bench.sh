@@ -1,7 +1,8 @@
 #!/bin/bash
 # Runs on the GPU box (under gpurun): the plain bench first, then the ncu launch list of the same command
-# (index-construction kernels filtered out by name: ~350 k launches that are outside the timed region) and one
-# `--set full` capture of the search kernel.  Outputs land in gpurun_out/; summaries are copied to profiles/ by hand.
+# (index-construction kernels filtered out by name: ~350 k launches that are outside the timed region), one
+# `--set full` capture of the search kernel and one of the tcgen05 ground-truth kernel (tools/gt_bench.py).
+# Outputs land in gpurun_out/; summaries are copied to profiles/ by hand (tools/ncu_summary.py).
 set -u
 tag="${1:-r01}"
 shift || true
@@ -14,5 +15,8 @@ ncu --metrics gpu__time_duration.sum --clock-control none -k 'regex:hnsw_search|
     --csv --log-file $out/launches_$tag.csv $cmd > $out/ncu_launches_$tag.log 2>&1
 echo "launch list rc=$?"
 ncu --set full --clock-control none --import-source on -k 'regex:hnsw_search' -s 4 -c 2 -f -o $out/search_$tag $cmd > $out/ncu_full_$tag.log 2>&1
-echo "full capture rc=$?"
+echo "full capture (search) rc=$?"
+gcmd="python tools/gt_bench.py 10000000 10000 10 1 mma"
+$gcmd > $out/gt_plain_$tag.json 2>&1 && ncu --set full --clock-control none --import-source on -k 'regex:gt_mma' -s 1 -c 1 -f -o $out/gt_$tag $gcmd > $out/ncu_gt_$tag.log 2>&1
+echo "full capture (ground truth) rc=$?"
 ls -la $out
