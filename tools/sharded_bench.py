@@ -59,7 +59,7 @@ res["ground_truth"]["sha"] = __import__("hashlib").sha256(gtk.tobytes()).hexdige
 
 # sharded HNSW over this rank's rows
 t0 = time.time()
-idx = hb.build_hnsw(d.cpu().numpy().view(np.uint64), 96, 24, 256, rayon_threads=16, keep_host=False)
+idx = hb.build_hnsw(d.cpu().numpy().view(np.uint64), 96, 24, 256, rayon_threads=16, keep_host=False, device=lr)
 res["index_build_s"] = time.time() - t0
 ms, packed = timed(lambda: sharded.knns_sharded(idx, start, q, K, EF))
 keys = packed.cpu().numpy().view(np.uint64) & np.uint64(0xFFFFFFFF)
