@@ -60,6 +60,10 @@ struct SearchCounters {
 #define HB_GATHER_CPASYNC 1
 #endif
 constexpr uint32_t kStageBytes = HB_GATHER_CPASYNC ? 32u * 128u : 0u;
+// 1 = the next group's sketch gather is issued before the accept replay of the current group (same results)
+#ifndef HB_OVERLAP_REPLAY
+#define HB_OVERLAP_REPLAY 1
+#endif
 
 // per-warp scratch in shared memory: [stage 4 KB][cache 4 << cache_log2][ids kIdsCap * 4]
 struct WarpScratch {
@@ -262,7 +266,17 @@ struct BeamHeap {
     key = bm_key(c);
     return true;
   }
-  __device__ __forceinline__ void peek_unexpanded2(uint32_t& k1, uint32_t& k2) const { k1 = k2 = kNoKey; }
+  // the element pop_unexpanded() would return next if nothing were inserted in between (prefetch prediction; k2 unused)
+  __device__ __forceinline__ void peek_unexpanded2(uint32_t& k1, uint32_t& k2) const {
+    uint64_t cv = kBeamInf;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+      if (!(w[r] & 1ull) && w[r] < cv) cv = w[r];
+    const uint32_t mh = __reduce_min_sync(kFullMask, hi32(cv));
+    const uint32_t ml = __reduce_min_sync(kFullMask, hi32(cv) == mh ? lo32(cv) : 0xFFFFFFFFu);
+    k1 = (mh == 0xFFFFFFFFu) ? kNoKey : bm_key(((uint64_t)mh << 32) | ml);
+    k2 = kNoKey;
+  }
 
   // w.push(v); if |w| > ef: w.pop_max()  (nsw.rs:171-176).  Precondition: v not in w, and (size < ef or v < maxv).
   // Returns the evicted element (kBeamInf when nothing was evicted).
@@ -321,6 +335,47 @@ struct BeamHeap {
     return __shfl_sync(kFullMask, t, i & 31u);
   }
 };
+
+#if HB_GATHER_CPASYNC
+// hamming32() in two halves, so that the accept replay of one group of 32 runs while the next group's rows are in
+// flight: issue = the cp.async copies (every lane copies exactly the 16-B pieces it reads back), finish = wait, XOR+POPC,
+// butterfly.  finish() has consumed the stage (its shuffles need every piece) before the next issue() is reached.
+__device__ __forceinline__ void hamming32_issue(const uint4* __restrict__ sk, const uint32_t* ids, uint32_t n, uint4* stage) {
+  const uint32_t lane = threadIdx.x & 31, g = lane >> 3, s = lane & 7u;
+  uint4* const mine = stage + g * 8 + s;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (4u * j < n) {
+      const uint4* src = sk + (size_t)ids[min(4u * j + g, n - 1u)] * 8 + s;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(mine + j * 32)), "l"(src) : "memory");
+    }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t hamming32_finish(uint32_t n, uint4 qv, const uint4* stage) {
+  const uint32_t lane = threadIdx.x & 31, g = lane >> 3, s = lane & 7u;
+  const uint4* const mine = stage + g * 8 + s;
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  uint32_t x[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) x[j] = (4u * j < n) ? popc_xor4(mine[j * 32], qv) : 0u;
+  const bool b0 = s & 1u, b1 = s & 2u, b2 = s & 4u;
+  uint32_t y[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t keep = b0 ? x[2 * i + 1] : x[2 * i], send = b0 ? x[2 * i] : x[2 * i + 1];
+    y[i] = keep + __shfl_xor_sync(kFullMask, send, 1);
+  }
+  uint32_t z[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const uint32_t keep = b1 ? y[2 * i + 1] : y[2 * i], send = b1 ? y[2 * i] : y[2 * i + 1];
+    z[i] = keep + __shfl_xor_sync(kFullMask, send, 2);
+  }
+  const uint32_t keep = b2 ? z[1] : z[0], send = b2 ? z[0] : z[1];
+  const uint32_t t = keep + __shfl_xor_sync(kFullMask, send, 4);
+  return __shfl_sync(kFullMask, t, 8u * (lane & 3u) + (lane >> 2));  // row i sits in lane 8 * (i % 4) + i / 4
+}
+#endif
 
 // Distances of the n (1..32) sketches whose gids are staged in ids[0..n) to the query piece qv:
 // lane i returns the distance of ids[i] (garbage for i >= n).  Lane = (g = lane / 8, s = lane % 8) owns the
@@ -548,11 +603,19 @@ __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint3
       __syncwarp();
       HB_TICK(t_chk1);
       HB_ACC(c.E, t_chk0, t_chk1);
+#if HB_GATHER_CPASYNC && HB_OVERLAP_REPLAY
+      if (n_new) hamming32_issue(gv.sk, ws.ids, min(32u, n_new), ws.stage);
+#endif
       for (uint32_t g0 = 0; g0 < n_new; g0 += 32) {
         const uint32_t n = min(32u, n_new - g0);
         HB_TICK(t_g0);
         const uint32_t myid = ws.ids[g0 + (lane < n ? lane : 0u)];
+#if HB_GATHER_CPASYNC && HB_OVERLAP_REPLAY
+        const uint32_t myd = hamming32_finish(n, qv, ws.stage);  // nsw.rs:164-165
+        if (g0 + 32 < n_new) hamming32_issue(gv.sk, ws.ids + g0 + 32, min(32u, n_new - g0 - 32), ws.stage);  // in flight during the replay
+#else
         const uint32_t myd = hamming32(gv.sk, ws.ids + g0, n, qv, ws.stage);  // nsw.rs:164-165
+#endif
         if (!sk_done) {
           prefetch_row_sketches(gv.sk, pw0, pw1);
           sk_done = true;
