@@ -142,30 +142,40 @@ struct GtParams {
   uint32_t n_qtiles, n_chunks, tiles_per_chunk, n_tiles;
 };
 
-// k > 16: single-thread insert into the thread's ascending list in global memory (binary search for the slot, then the
-// tail moves up in batches of independent loads); returns the new accumulator threshold
-__device__ __noinline__ int gt_insert(uint64_t* list, uint32_t k, int popq, int acc, uint32_t key, int T, uint32_t* gthr) {
+// k > 16: the row's list lives in global memory, UNSORTED (slots [0, cnt) filled, the rest kNone; the merge kernel
+// does not need order).  While it is filling, an accepted row is one store.  Once full, the caller's threshold admits
+// only rows strictly nearer than the list's maximum: one pass of independent loads (32 in flight) finds the maximum's
+// slot and the runner-up, the row replaces the maximum, and the new threshold is max(runner-up, row).
+// Returns the new accumulator threshold.
+__device__ __noinline__ int gt_insert(uint64_t* list, uint32_t k, uint32_t& cnt, int popq, int acc, uint32_t key, int T, uint32_t* gthr) {
   const uint64_t v = ((uint64_t)(uint32_t)(popq - (acc >> 6)) << 32) | key;
-  if (v >= list[k - 1]) return T;
-  uint32_t lo = 0, hi = k - 1;  // first index whose element exceeds v is in [lo, hi]
-  while (lo < hi) {
-    const uint32_t mid = (lo + hi) >> 1;
-    if (list[mid] > v) hi = mid;
-    else lo = mid + 1;
+  const bool filling = cnt < k;
+  if (filling) {
+    list[cnt++] = v;
+    if (cnt < k) return T;
   }
-  uint32_t i = k - 1;
-  while (i >= lo + 8) {
-    uint64_t e[8];
+  uint64_t m1 = 0, m2 = 0;
+  uint32_t p1 = 0;
+  for (uint32_t base = 0; base < k; base += 32) {
+    uint64_t e[32];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) e[j] = list[i - 1 - j];
+    for (int j = 0; j < 32; ++j) e[j] = (base + j < k) ? list[base + j] : 0ull;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) list[i - j] = e[j];
-    i -= 8;
+    for (int j = 0; j < 32; ++j) {
+      if (e[j] > m1) {
+        m2 = m1;
+        m1 = e[j];
+        p1 = base + j;
+      } else if (e[j] > m2) {
+        m2 = e[j];
+      }
+    }
   }
-  for (; i > lo; --i) list[i] = list[i - 1];
-  list[lo] = v;
-  const uint64_t last = list[k - 1];
-  if (last == kNone) return INT_MIN;
+  uint64_t last = m1;
+  if (!filling) {
+    list[p1] = v;  // v < m1: its distance is strictly below the maximum's
+    last = v > m2 ? v : m2;
+  }
   atomicMin(gthr, (uint32_t)(last >> 32));
   return 64 * (popq - (int)(uint32_t)(last >> 32));
 }
@@ -221,6 +231,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
       // k <= 16: the row's ascending list lives in registers, right-aligned (rl[16-k..15]; the slots before it hold 0,
       // which no element displaces), so the k-th best is always rl[15] and every index is static
       uint64_t rl[kRegList ? 16 : 1];
+      uint32_t cnt = 0;  // k > 16: filled slots of the row's (unsorted) list in global memory
       int popq = 0;
       if (live) {
         const uint4* qp = reinterpret_cast<const uint4*>(p.queries + (size_t)q * 16);
@@ -308,7 +319,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
                       T = 64 * (popq - (int)(uint32_t)(last >> 32));
                     }
                   } else {
-                    T = gt_insert(list, p.k, popq, x, key, T, gq);
+                    T = gt_insert(list, p.k, cnt, popq, x, key, T, gq);
                   }
                   Te = max(T, Tg);
                 }
@@ -569,7 +580,7 @@ void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset
     const uint64_t waves = (items + sms - 1) / sms;
     // cost model: waves x (tiles per chunk + per-item overhead: writing the query tile and refilling the item's lists,
     // in tile times -- register lists (k <= 16) refill in ~25, lists in global memory in ~4 per entry)
-    const double overhead = 2.0 + (k <= 16 ? 25.0 : 4.0 * k);
+    const double overhead = 2.0 + (k <= 16 ? 25.0 : 0.5 * k);
     const double cost = (double)waves * (tpc + overhead);
     const double eff = ((double)p.n_tiles * p.n_qtiles / sms) / cost;
     if (eff > best_eff + 1e-9) {
@@ -600,7 +611,7 @@ void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) {
     try {
-      topk_merge_device(partial, p.n_chunks, nq, k, d_packed, stream);
+      topk_merge_device(partial, p.n_chunks, nq, k, d_packed, stream, /*sorted=*/k <= 16);
     } catch (...) {
       cudaFreeAsync(partial, stream);
       throw;

@@ -128,7 +128,8 @@ void ground_truth_scan_device(const void* d_data, uint64_t n, uint64_t key_offse
 bool ground_truth_mma_supported(const void* d_data, const void* d_queries, uint64_t n, uint64_t nq, uint32_t k);
 void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
                              void* d_packed, cudaStream_t stream);
-void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream);
+void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream,
+                       bool sorted = true);  // !sorted: the input lists are in any order (kNone = no entry)
 void unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists, cudaStream_t stream);
 void pack_device(const void* d_keys, const void* d_dists, const void* d_found, uint64_t nq, uint32_t k, uint64_t key_offset,
                  void* d_packed, cudaStream_t stream);

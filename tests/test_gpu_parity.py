@@ -312,3 +312,36 @@ def test_sharded_hnsw_pack_and_merge(hb, oracle):
     gt = sharded.ground_truth_sharded(dd, 0, dq, k)
     gk, gd = oracle.ground_truth(data, q, k)
     assert np.array_equal(gt.cpu().numpy().view(np.uint64), (gd << np.uint64(32)) | gk)
+
+
+@pytest.mark.parametrize("k", [10, 100])
+def test_ground_truth_large_properties(hb, k):
+    """Size-independent checks at a size the oracle would not finish in seconds (2 M x 1 k, generated on the device):
+    tcgen05 kernel == scan kernel bit for bit; rows ascend in (distance, key) with unique keys; every returned distance
+    is recomputed from the sketches; queries that are data rows find themselves at distance 0."""
+    import torch
+    from hnsw_itu_b200 import _lib
+    n, nq = 2_000_000, 1024
+    d = torch.empty((n, 16), dtype=torch.int64, device="cuda")
+    q = torch.empty((nq, 16), dtype=torch.int64, device="cuda")
+    hb.synth_sketches(d.data_ptr(), n, 1003)
+    hb.synth_sketches(q.data_ptr(), nq, 1004)
+    members = torch.arange(0, 64, device="cuda") * 31_013 + 7          # 64 queries are copies of data rows
+    q[:64] = d[members]
+    out = {}
+    for algo in (2, 1):
+        p = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+        _lib.check(_lib.lib().hb_ground_truth_device_algo(d.data_ptr(), n, 0, q.data_ptr(), nq, k, algo, p.data_ptr(), None))
+        torch.cuda.synchronize()
+        out[algo] = p.cpu().numpy().view(np.uint64)
+    assert np.array_equal(out[1], out[2])
+    packed = out[2]
+    assert (packed[:, 1:] > packed[:, :-1]).all()                       # strictly ascending (distance << 32 | key): unique keys
+    keys, dists = (packed & np.uint64(0xFFFFFFFF)).astype(np.int64), (packed >> np.uint64(32)).astype(np.int64)
+    assert keys.max() < n
+    hd, hq = d.cpu().numpy().view(np.uint64), q.cpu().numpy().view(np.uint64)
+    rows = np.arange(0, nq, 7)
+    x = hd[keys[rows]] ^ hq[rows][:, None, :]                           # (r, k, 16)
+    ref = np.unpackbits(x.view(np.uint8), axis=-1).sum(-1)
+    assert np.array_equal(ref, dists[rows])
+    assert (dists[:64, 0] == 0).all() and (keys[:64, 0] <= members.cpu().numpy()).all()
