@@ -104,21 +104,22 @@ __global__ void __launch_bounds__(kScanWarps * 32) scan_topk_kernel(const uint4*
   }
 }
 
-// one warp per query: exact merge of n_lists lists of k (ascending, or in any order when !sorted; kNone = no entry)
+// one warp per query: exact merge of n_lists lists of `width` slots (ascending with width == k, or in any order when
+// !sorted; kNone = no entry) into the k smallest
 __global__ void __launch_bounds__(128) topk_merge_kernel(const uint64_t* __restrict__ lists, uint32_t n_lists, uint64_t nq, uint32_t k,
-                                                         uint32_t sorted, uint64_t* __restrict__ out) {
+                                                         uint32_t sorted, uint32_t width, uint64_t* __restrict__ out) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   uint64_t* list = reinterpret_cast<uint64_t*>(smem_raw) + (size_t)wib * k;
   const uint64_t q = (uint64_t)blockIdx.x * 4 + wib;
   if (q >= nq) return;
-  for (uint32_t i = lane; i < k; i += 32) list[i] = sorted ? lists[q * k + i] : kNone;
+  for (uint32_t i = lane; i < k; i += 32) list[i] = sorted ? lists[q * width + i] : kNone;
   __syncwarp();
   for (uint32_t l = sorted ? 1 : 0; l < n_lists; ++l) {
-    const uint64_t* src = lists + ((size_t)l * nq + q) * k;
-    for (uint32_t base = 0; base < k; base += 32) {
+    const uint64_t* src = lists + ((size_t)l * nq + q) * width;
+    for (uint32_t base = 0; base < width; base += 32) {
       const uint32_t i = base + lane;
-      const uint64_t cand = (i < k) ? src[i] : kNone;
+      const uint64_t cand = (i < width) ? src[i] : kNone;
       uint32_t pm = __ballot_sync(kFull, cand < list[k - 1]);
       if (!pm) {
         if (sorted) break;  // src ascending: nothing further can qualify
@@ -167,14 +168,17 @@ void pack_device(const void* d_keys, const void* d_dists, const void* d_found, u
   HB_CUDA(cudaGetLastError());
 }
 
-void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream, bool sorted) {
+void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream, bool sorted,
+                       uint32_t width) {
+  if (width == 0) width = k;
+  HB_REQUIRE(!sorted || width == k, HB_ERR_INVALID, "ascending lists have exactly k slots");
   HB_REQUIRE(k >= 1 && k <= HB_MAX_K, HB_ERR_INVALID, "k out of range");
   HB_REQUIRE(n_lists >= 1, HB_ERR_INVALID, "need at least one list");
   if (nq == 0) return;
   const size_t smem = (size_t)4 * k * 8;
   HB_CUDA(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   topk_merge_kernel<<<(unsigned)((nq + 3) / 4), 128, smem, stream>>>(static_cast<const uint64_t*>(d_lists), n_lists, nq, k,
-                                                                     sorted ? 1u : 0u, static_cast<uint64_t*>(d_out));
+                                                                     sorted ? 1u : 0u, width, static_cast<uint64_t*>(d_out));
     count_launches();
   HB_CUDA(cudaGetLastError());
 }

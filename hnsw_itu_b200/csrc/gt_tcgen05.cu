@@ -135,49 +135,42 @@ constexpr uint32_t kTr0 = 3000;
 struct GtParams {
   const uint64_t* data;     // n rows x 16 u64
   const uint64_t* queries;  // nq rows x 16 u64
-  uint64_t* partial;        // (n_chunks, nq, k) packed ascending lists
+  uint64_t* partial;        // (n_chunks, nq, lcap) packed lists
   uint32_t* gthr;           // per query: smallest k-th best distance any work item has reached so far (bound on the global k-th)
   uint64_t n, key_offset;
   uint32_t nq, k;
+  uint32_t lcap;            // slots per row list in `partial`: k (k <= 16, ascending) or 2k (k > 16, unordered append buffer)
   uint32_t n_qtiles, n_chunks, tiles_per_chunk, n_tiles;
 };
 
-// k > 16: the row's list lives in global memory, UNSORTED (slots [0, cnt) filled, the rest kNone; the merge kernel
-// does not need order).  While it is filling, an accepted row is one store.  Once full, the caller's threshold admits
-// only rows strictly nearer than the list's maximum: one pass of independent loads (32 in flight) finds the maximum's
-// slot and the runner-up, the row replaces the maximum, and the new threshold is max(runner-up, row).
-// Returns the new accumulator threshold.
-__device__ __noinline__ int gt_insert(uint64_t* list, uint32_t k, uint32_t& cnt, int popq, int acc, uint32_t key, int T, uint32_t* gthr) {
-  const uint64_t v = ((uint64_t)(uint32_t)(popq - (acc >> 6)) << 32) | key;
-  const bool filling = cnt < k;
-  if (filling) {
-    list[cnt++] = v;
-    if (cnt < k) return T;
+// k > 16: the row's candidates go to an UNORDERED append buffer of 2k slots in global memory (one store per accepted
+// row; the merge kernel needs no order).  When a buffer fills, the whole warp compacts it: the k-th smallest packed
+// value V is found by bisection on the 43 significant bits (every lane counts its share, REDUX adds), entries <= V
+// move to the front, the tail is cleared, and the row's threshold becomes V's distance.  Amortised over k appends,
+// against a dependent chain of loads per insert into a sorted list.  `buf` and the result are warp-uniform.
+__device__ __noinline__ uint64_t gt_warp_compact(uint64_t* buf, uint32_t cap, uint32_t k) {
+  const uint32_t lane = threadIdx.x & 31;
+  uint64_t lo = 0, hi = (1025ull << 32);  // smallest V with count(e <= V) >= k lies in [lo, hi]
+  while (lo < hi) {
+    const uint64_t mid = lo + ((hi - lo) >> 1);
+    uint32_t c = 0;
+    for (uint32_t i = lane; i < cap; i += 32) c += (buf[i] <= mid) ? 1u : 0u;
+    c = __reduce_add_sync(0xFFFFFFFFu, c);
+    if (c >= k) hi = mid;
+    else lo = mid + 1;
   }
-  uint64_t m1 = 0, m2 = 0;
-  uint32_t p1 = 0;
-  for (uint32_t base = 0; base < k; base += 32) {
-    uint64_t e[32];
-#pragma unroll
-    for (int j = 0; j < 32; ++j) e[j] = (base + j < k) ? list[base + j] : 0ull;
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      if (e[j] > m1) {
-        m2 = m1;
-        m1 = e[j];
-        p1 = base + j;
-      } else if (e[j] > m2) {
-        m2 = e[j];
-      }
-    }
+  uint32_t woff = 0;
+  for (uint32_t base = 0; base < cap; base += 32) {
+    const uint32_t i = base + lane;
+    const uint64_t e = (i < cap) ? buf[i] : kNone;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, e <= lo);
+    if (e <= lo) buf[woff + __popc(m & ((1u << lane) - 1u))] = e;  // woff + rank <= i: never ahead of the reads
+    woff += __popc(m);
+    __syncwarp();
   }
-  uint64_t last = m1;
-  if (!filling) {
-    list[p1] = v;  // v < m1: its distance is strictly below the maximum's
-    last = v > m2 ? v : m2;
-  }
-  atomicMin(gthr, (uint32_t)(last >> 32));
-  return 64 * (popq - (int)(uint32_t)(last >> 32));
+  for (uint32_t i = woff + lane; i < cap; i += 32) buf[i] = kNone;
+  __syncwarp();
+  return lo;
 }
 
 template <bool kRegList>
@@ -227,11 +220,11 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
       const uint32_t q = qtile * kTileM + row;
       const bool live = q < p.nq;
-      uint64_t* list = p.partial + ((size_t)chunk * p.nq + (live ? q : 0)) * p.k;
+      uint64_t* list = p.partial + ((size_t)chunk * p.nq + (live ? q : 0)) * p.lcap;
       // k <= 16: the row's ascending list lives in registers, right-aligned (rl[16-k..15]; the slots before it hold 0,
       // which no element displaces), so the k-th best is always rl[15] and every index is static
       uint64_t rl[kRegList ? 16 : 1];
-      uint32_t cnt = 0;  // k > 16: filled slots of the row's (unsorted) list in global memory
+      uint32_t cnt = 0;  // k > 16: filled slots of the row's append buffer
       int popq = 0;
       if (live) {
         const uint4* qp = reinterpret_cast<const uint4*>(p.queries + (size_t)q * 16);
@@ -241,7 +234,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
           popq += __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w);
         }
         if (!kRegList)
-          for (uint32_t i = 0; i < p.k; ++i) list[i] = kNone;
+          for (uint32_t i = 0; i < p.lcap; ++i) list[i] = kNone;
       }
       if (kRegList) {
 #pragma unroll
@@ -319,9 +312,24 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mma_kernel(const GtParams p) {
                       T = 64 * (popq - (int)(uint32_t)(last >> 32));
                     }
                   } else {
-                    T = gt_insert(list, p.k, cnt, popq, x, key, T, gq);
+                    list[cnt++] = ((uint64_t)(uint32_t)(popq - (x >> 6)) << 32) | key;
                   }
                   Te = max(T, Tg);
+                }
+                if (!kRegList) {  // warp-uniform: compact every buffer that just filled
+                  uint32_t fm = __ballot_sync(0xFFFFFFFFu, cnt == p.lcap);
+                  while (fm) {
+                    const int src = __ffs((int)fm) - 1;
+                    fm &= fm - 1;
+                    uint64_t* buf = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, reinterpret_cast<unsigned long long>(list), src));
+                    const uint64_t kth = gt_warp_compact(buf, p.lcap, p.k);
+                    if ((int)lane == src) {
+                      cnt = p.k;
+                      atomicMin(gq, (uint32_t)(kth >> 32));
+                      T = 64 * (popq - (int)(uint32_t)(kth >> 32));
+                      Te = max(T, Tg);
+                    }
+                  }
                 }
               }
             }
@@ -580,7 +588,7 @@ void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset
     const uint64_t waves = (items + sms - 1) / sms;
     // cost model: waves x (tiles per chunk + per-item overhead: writing the query tile and refilling the item's lists,
     // in tile times -- register lists (k <= 16) refill in ~25, lists in global memory in ~4 per entry)
-    const double overhead = 2.0 + (k <= 16 ? 25.0 : 0.5 * k);
+    const double overhead = 2.0 + (k <= 16 ? 25.0 : 0.25 * k);
     const double cost = (double)waves * (tpc + overhead);
     const double eff = ((double)p.n_tiles * p.n_qtiles / sms) / cost;
     if (eff > best_eff + 1e-9) {
@@ -593,7 +601,8 @@ void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset
   p.n_chunks = (p.n_tiles + p.tiles_per_chunk - 1) / p.tiles_per_chunk;
 
   uint64_t* partial = nullptr;
-  const size_t list_bytes = (size_t)p.n_chunks * nq * k * 8;
+  p.lcap = k <= 16 ? k : 2 * k;
+  const size_t list_bytes = (size_t)p.n_chunks * nq * p.lcap * 8;
   HB_CUDA(cudaMallocAsync(&partial, list_bytes + nq * 4, stream));
   p.partial = partial;
   p.gthr = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(partial) + list_bytes);
@@ -611,7 +620,7 @@ void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) {
     try {
-      topk_merge_device(partial, p.n_chunks, nq, k, d_packed, stream, /*sorted=*/k <= 16);
+      topk_merge_device(partial, p.n_chunks, nq, k, d_packed, stream, /*sorted=*/k <= 16, p.lcap);
     } catch (...) {
       cudaFreeAsync(partial, stream);
       throw;

@@ -129,7 +129,7 @@ bool ground_truth_mma_supported(const void* d_data, const void* d_queries, uint6
 void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
                              void* d_packed, cudaStream_t stream);
 void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream,
-                       bool sorted = true);  // !sorted: the input lists are in any order (kNone = no entry)
+                       bool sorted = true, uint32_t width = 0);  // !sorted: lists of `width` (default k) slots in any order, kNone = none
 void unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists, cudaStream_t stream);
 void pack_device(const void* d_keys, const void* d_dists, const void* d_found, uint64_t nq, uint32_t k, uint64_t key_offset,
                  void* d_packed, cudaStream_t stream);
