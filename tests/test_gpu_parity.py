@@ -345,3 +345,29 @@ def test_ground_truth_large_properties(hb, k):
     ref = np.unpackbits(x.view(np.uint8), axis=-1).sum(-1)
     assert np.array_equal(ref, dists[rows])
     assert (dists[:64, 0] == 0).all() and (keys[:64, 0] <= members.cpu().numpy()).all()
+
+
+def test_knns_pinned_buffers_used_in_place(hb, oracle):
+    """hb_knns with page-locked caller buffers (what a serving loop passes): the kernel reads the queries and writes
+    the results in host memory directly; same ids, distances and found counts as the staged path and the oracle."""
+    import ctypes as C
+    import torch
+    from hnsw_itu_b200 import _lib
+    data = oracle.synth(20000, 81)
+    q = oracle.synth(300, 82)
+    oidx = oracle.build(data, "hnsw", efc=48, m=12, M=64, parallel=False)
+    hidx = _to_gpu(hb, oidx, keep_host=False)
+    k, ef = 10, 64
+    hq = torch.from_numpy(q.view(np.int64)).pin_memory()
+    hk = torch.full((len(q), k), -1, dtype=torch.int64).pin_memory()
+    hd = torch.full((len(q), k), -1, dtype=torch.int64).pin_memory()
+    hf = torch.full((len(q),), -1, dtype=torch.int32).pin_memory()
+    u64p, u32p = C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)
+    for _ in range(2):
+        _lib.check(_lib.lib().hb_knns(hidx._h, C.cast(hq.data_ptr(), u64p), len(q), k, ef, 0, C.cast(hk.data_ptr(), u64p),
+                                      C.cast(hd.data_ptr(), u64p), C.cast(hf.data_ptr(), u32p), None))
+    ok, od, of = oidx.knns(q, k, ef)
+    assert np.array_equal(hk.numpy().view(np.uint64), ok) and np.array_equal(hd.numpy().view(np.uint64), od)
+    assert np.array_equal(hf.numpy().view(np.uint32), of)
+    gk, gd, gf = hidx.knns_arrays(q, k, ef)                              # pageable numpy buffers: staged copies
+    assert np.array_equal(gk, ok) and np.array_equal(gd, od) and np.array_equal(gf, of)
