@@ -1,0 +1,645 @@
+// gt_mxf4.cu -- the `ground-truth` GEMM of gt_tcgen05.cu with 4-bit operands: tcgen05.mma kind::mxf4 (block-scaled
+// E2M1, all scale factors 1.0).  Same identity, Hamming(q, d) = pop(q) - sum_i (2 q_i - 1) d_i, same pipeline, same
+// fused top-k; what changes is the operand encoding and therefore the three resources that paced the int8 kernel:
+//   * the tensor pipe runs K = 64 per instruction instead of 32 (half the MMA time per tile),
+//   * a data row expands to 512 bytes instead of 1024 (half the shared-memory stores, 5 logic ops per 32 elements),
+//   * the query tile takes 64 KB instead of 128 KB, which buys five pipeline stages instead of three.
+// E2M1 holds +-{0.5, 1, 2} exactly: data bit at nibble position u -> {0.5, 1, 2, 2}, query bit -> +-{2, 1, 0.5, 0.5}, so every
+// product is +-1 or 0 and the fp32 accumulator holds the integer pop(q) - Hamming exactly (|acc| <= 1024).  Both
+// operands use the same physical nibble layout, so the K permutation this implies cancels.  The block scale factors
+// (E8M0, one per 32 elements) are all 0x7F = 2^0: sixteen TMEM columns are filled with that byte once, and since every
+// byte is equal the scale-factor layout does not matter.  Accumulator tiles are 128 x 240 (two of them + the scale
+// columns = 512 TMEM columns).  Everything else -- roles, barriers, lists, threshold sharing, merge -- is gt_tcgen05.cu's.
+#include <algorithm>
+#include <climits>
+
+#include "hb_internal.h"
+
+namespace hb {
+namespace {
+
+constexpr uint64_t kNone = ~0ull;
+constexpr int kTileM = 128;   // queries per work item (UMMA M)
+constexpr int kTileN = 240;   // data rows per accumulator tile (UMMA N): 2 x 240 + 16 scale-factor columns <= 512
+constexpr int kGroup = 48;      // accumulator columns an epilogue thread reads per step (240 = 5 x 48)
+constexpr int kStageRows = 256; // rows a stage buffer holds (the last 16 are never written or read)
+constexpr uint32_t kAccStride = 256, kSfCol = 496;  // TMEM columns: accumulators at 0 and 256, scale factors at 496..511
+constexpr int kKBlocks = 4;   // 1024 bits = 4 K-blocks of 256 E2M1 (one 128-B swizzle atom row each)
+constexpr int kStages = 5;
+constexpr int kEpiWarps = 4, kExpWarps = 8;
+constexpr int kThreads = (kEpiWarps + kExpWarps + 1) * 32;
+constexpr uint32_t kABytes = kTileM * 512;            // 4 K-blocks x (128 rows x 128 B)
+constexpr uint32_t kAKBlockBytes = kTileM * 128;
+constexpr uint32_t kStageBytes = kStageRows * 128;
+constexpr uint32_t kBarOffset = kABytes + kStages * kStageBytes;
+constexpr uint32_t kSmemBytes = kBarOffset + 192 + 1024;  // + barriers + alignment slack
+
+// instruction descriptor (cute::UMMA::InstrDescriptorBlockScaled layout): A = B = E2M1 (MXF4 format 1), both K-major,
+// scale format E8M0, scale-factor ids 0, N = 240, M = 128, K = 64
+constexpr uint32_t kIdesc = (1u << 7) | (1u << 10) | (1u << 23) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded spin: a protocol bug traps (the launch fails with an error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  long long t0 = 0;
+  for (uint32_t spins = 0; !done; ++spins) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (!done && (spins & 1023u) == 1023u) {
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 6000000000ll) __trap();  // ~3 s: no wait in this kernel is longer than a few ms
+    }
+  }
+}
+
+// K-major, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart (cute::UMMA::SmemDescriptor layout, version 1)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+
+__device__ __forceinline__ void umma_mxf4(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t tmem_sf, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%5], p;\n\t}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(kIdesc), "r"(accumulate), "r"(tmem_sf)
+      : "memory");
+}
+// one lane of the (converged) warp; ptxas knows the guarded region is single-threaded, so UTCIMMA needs no lane loop
+__device__ __forceinline__ uint32_t elect_one_sync() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, %1;\n\t"
+      "@px mov.s32 %0, 1;\n\t}"
+      : "+r"(pred)
+      : "r"(0xFFFFFFFFu));
+  return pred;
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+#define HB_TMEM_LD32(v, taddr)                                                                                          \
+  asm volatile(                                                                                                         \
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                         \
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "                                         \
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"                         \
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),     \
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),          \
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),         \
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                       \
+      : "r"(taddr)                                                                                                      \
+      : "memory")
+
+#ifdef HB_GT_DIAG
+// per-CTA phase clocks (diagnostic build only, tools/gt_diag.py): [0] kernel cycles, [1] MMA warp waiting for a free
+// accumulator, [2] MMA warp waiting for a full stage, [3] expansion warp 0 waiting for an empty stage, [4] its fences,
+// [5] epilogue warp 0 waiting for a full accumulator, [6] its inserts, [7] tiles, [8] expansion waiting for A free
+__device__ long long g_gt4_diag[256 * 16];
+// trace of CTA 0, tiles [kTr0, kTr0+32): at g_gt4_diag[2400 + 32*(tile-kTr0) + slot]
+//   slot 0 MMA passes acc-free wait, 1 MMA issued last stage, 2+w epilogue warp w sees acc full, 6+w warp w releases acc,
+//   10+kb expansion warp 0 arrives stage kb, 18+kb MMA passes full wait of stage kb
+constexpr uint32_t kTr0 = 3000;
+#define HB_TRACE(tile, slot) \
+  do { if (blockIdx.x == 0 && (tile) >= kTr0 && (tile) < kTr0 + 32 && (threadIdx.x & 31) == 0) g_gt4_diag[2400 + 32 * ((tile) - kTr0) + (slot)] = clock64(); } while (0)
+#define HB_DIAG_T0() const long long dg_t0 = clock64()
+#define HB_DIAG_ADD(var) var += clock64() - dg_t0
+#else
+#define HB_TRACE(tile, slot)
+#define HB_DIAG_T0()
+#define HB_DIAG_ADD(var)
+#endif
+
+#define HB_TMEM_LD16(v, taddr)                                                                                          \
+  asm volatile(                                                                                                         \
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "                                                                         \
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"                                  \
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),     \
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])                        \
+      : "r"(taddr)                                                                                                      \
+      : "memory")
+
+struct GtParams {
+  const uint64_t* data;     // n rows x 16 u64
+  const uint64_t* queries;  // nq rows x 16 u64
+  uint64_t* partial;        // (n_chunks, nq, lcap) packed lists
+  uint32_t* gthr;           // per query: smallest k-th best distance any work item has reached so far (bound on the global k-th)
+  uint64_t n, key_offset;
+  uint32_t nq, k;
+  uint32_t lcap;            // slots per row list in `partial`: k (k <= 16, ascending) or 2k (k > 16, unordered append buffer)
+  uint32_t n_qtiles, n_chunks, tiles_per_chunk, n_tiles;
+};
+
+// k > 16: the row's candidates go to an UNORDERED append buffer of 2k slots in global memory (one store per accepted
+// row; the merge kernel needs no order).  When a buffer fills, the whole warp compacts it: the k-th smallest packed
+// value V is found by bisection on the 43 significant bits (every lane counts its share, REDUX adds), entries <= V
+// move to the front, the tail is cleared, and the row's threshold becomes V's distance.  Amortised over k appends,
+// against a dependent chain of loads per insert into a sorted list.  `buf` and the result are warp-uniform.
+__device__ __noinline__ uint64_t gt4_warp_compact(uint64_t* buf, uint32_t cap, uint32_t k) {
+  const uint32_t lane = threadIdx.x & 31;
+  uint64_t lo = 0, hi = (1025ull << 32);  // smallest V with count(e <= V) >= k lies in [lo, hi]
+  while (lo < hi) {
+    const uint64_t mid = lo + ((hi - lo) >> 1);
+    uint32_t c = 0;
+    for (uint32_t i = lane; i < cap; i += 32) c += (buf[i] <= mid) ? 1u : 0u;
+    c = __reduce_add_sync(0xFFFFFFFFu, c);
+    if (c >= k) hi = mid;
+    else lo = mid + 1;
+  }
+  uint32_t woff = 0;
+  for (uint32_t base = 0; base < cap; base += 32) {
+    const uint32_t i = base + lane;
+    const uint64_t e = (i < cap) ? buf[i] : kNone;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, e <= lo);
+    if (e <= lo) buf[woff + __popc(m & ((1u << lane) - 1u))] = e;  // woff + rank <= i: never ahead of the reads
+    woff += __popc(m);
+    __syncwarp();
+  }
+  for (uint32_t i = woff + lane; i < cap; i += 32) buf[i] = kNone;
+  __syncwarp();
+  return lo;
+}
+
+template <bool kRegList>
+__global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;  // swizzle atoms need 1024-B alignment
+  unsigned char* sm = smem_raw + (base - raw);
+  const uint32_t sA = base, sB = base + kABytes, sBar = base + kBarOffset;
+  // barriers: full[5] empty[5] tfull[2] tempty[2] a_full a_free (128 bytes), then the TMEM base slot
+  const uint32_t bFull = sBar, bEmpty = sBar + 8 * kStages, bTFull = sBar + 16 * kStages, bTEmpty = bTFull + 16, bAFull = bTEmpty + 16,
+                 bAFree = bAFull + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + kBarOffset + 128);
+
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(bFull + 8 * s, kExpWarps);
+      mbar_init(bEmpty + 8 * s, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(bTFull + 8 * a, 1);
+      mbar_init(bTEmpty + 8 * a, kEpiWarps * 32);
+    }
+    mbar_init(bAFull, kExpWarps);
+    mbar_init(bAFree, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+  // scale factors: E8M0 0x7F = 2^0 in every byte of TMEM columns 496..511, all 128 lanes; read by every MMA as SFA and SFB
+  if (warp < 4) {
+    const uint32_t one = 0x7F7F7F7Fu;
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(
+            tmem + ((warp * 32u) << 16) + kSfCol),
+        "r"(one)
+        : "memory");
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+  const uint32_t n_items = p.n_qtiles * p.n_chunks;
+
+  if (warp < kEpiWarps) {
+    // ===================== epilogue: thread = one query row of the accumulator =====================
+    const uint32_t row = warp * 32 + lane;
+    uint32_t tcount = 0;
+    [[maybe_unused]] long long dg_tfull = 0, dg_ins = 0;
+    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+      const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
+      const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
+      const uint32_t q = qtile * kTileM + row;
+      const bool live = q < p.nq;
+      uint64_t* list = p.partial + ((size_t)chunk * p.nq + (live ? q : 0)) * p.lcap;
+      // k <= 16: the row's ascending list lives in registers, right-aligned (rl[16-k..15]; the slots before it hold 0,
+      // which no element displaces), so the k-th best is always rl[15] and every index is static
+      uint64_t rl[kRegList ? 16 : 1];
+      uint32_t cnt = 0;  // k > 16: filled slots of the row's append buffer
+      int popq = 0;
+      if (live) {
+        const uint4* qp = reinterpret_cast<const uint4*>(p.queries + (size_t)q * 16);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint4 w = __ldg(qp + j);
+          popq += __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w);
+        }
+        if (!kRegList)
+          for (uint32_t i = 0; i < p.lcap; ++i) list[i] = kNone;
+      }
+      if (kRegList) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) rl[i] = ((uint32_t)i + p.k < 16u) ? 0ull : kNone;
+      }
+      // The accumulator must exceed T to beat this item's current k-th best (strict: keys ascend inside an item), and
+      // must exceed Tg to be at most the best k-th distance any item has reached for this query (ties kept: the
+      // other item's keys may be larger).  Rows failing either test cannot be in the global top-k.
+      float T = live ? -INFINITY : INFINITY;  // accumulators are exact small integers in fp32: pop(q) - Hamming
+      uint32_t* gq = p.gthr + (live ? q : 0);
+      const uint64_t row_end = min(p.n, (uint64_t)t1 * kTileN);
+      for (uint32_t t = t0; t < t1; ++t, ++tcount) {
+        const uint32_t acc = tcount & 1, use = tcount >> 1;
+        const uint32_t g_now = *reinterpret_cast<volatile uint32_t*>(gq);
+        {
+          HB_DIAG_T0();
+          mbar_wait(bTFull + 8 * acc, use & 1);
+          HB_DIAG_ADD(dg_tfull);
+        }
+        HB_TRACE(tcount, 2 + warp);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const float Tg = (g_now == 0xFFFFFFFFu) ? -INFINITY : (float)(popq - (int)g_now) - 1.0f;
+        float Te = fmaxf(T, Tg);
+        const uint32_t taddr = tmem + ((warp * 32u) << 16) + acc * kAccStride;
+        const uint64_t tile_row0 = (uint64_t)t * kTileN;
+#pragma unroll 1
+        for (int g = 0; g < kTileN / kGroup; ++g) {
+          uint32_t h0 = 0, h1 = 0;
+          bool hit;
+          {
+            uint32_t v[kGroup];
+            HB_TMEM_LD32(v, taddr + g * kGroup);
+            HB_TMEM_LD16((v + 32), taddr + g * kGroup + 32);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            float mx = __uint_as_float(v[0]);
+#pragma unroll
+            for (int c = 1; c < kGroup; c += 1) mx = fmaxf(mx, __uint_as_float(v[c]));
+            hit = __any_sync(0xFFFFFFFFu, mx > Te);
+            if (hit) {  // warp-uniform: which columns pass for which lane
+#pragma unroll
+              for (int c = 0; c < 32; ++c) h0 |= (uint32_t)(__uint_as_float(v[c]) > Te) << c;
+#pragma unroll
+              for (int c = 0; c < kGroup - 32; ++c) h1 |= (uint32_t)(__uint_as_float(v[32 + c]) > Te) << c;
+            }
+          }
+          if (hit) {
+            // Rare path, kept warp-uniform: for every column some lane wants, each lane re-reads its own value of that
+            // column from TMEM (the accumulator is still ours) and the lanes that pass run one copy of the insert.
+            HB_DIAG_T0();
+            const uint64_t r0 = tile_row0 + (uint64_t)g * kGroup;
+            const uint32_t nvalid = (uint32_t)min((uint64_t)kGroup, row_end > r0 ? row_end - r0 : 0);
+            uint64_t m = (uint64_t)__reduce_or_sync(0xFFFFFFFFu, h0) | ((uint64_t)__reduce_or_sync(0xFFFFFFFFu, h1) << 32);
+            if (nvalid < (uint32_t)kGroup) m &= (1ull << nvalid) - 1ull;
+            {
+              while (m) {
+                const uint32_t col = (uint32_t)__ffsll((long long)m) - 1u;
+                m &= m - 1;
+                uint32_t xb;
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(xb) : "r"(taddr + g * kGroup + col) : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                const float x = __uint_as_float(xb);
+                if (x > Te) {
+                  const uint32_t hd = (uint32_t)(popq - (int)x);
+                  const uint32_t key = (uint32_t)(p.key_offset + r0 + col);
+                  if (kRegList) {
+                    const uint64_t e = ((uint64_t)hd << 32) | key;
+#pragma unroll
+                    for (int i = 15; i > 0; --i) {
+                      if (rl[i - 1] > e) rl[i] = rl[i - 1];
+                      else if (rl[i] > e) rl[i] = e;
+                    }
+                    if (rl[0] > e) rl[0] = e;
+                    const uint64_t last = rl[15];
+                    if (last != kNone) {
+                      atomicMin(gq, (uint32_t)(last >> 32));
+                      T = (float)(popq - (int)(uint32_t)(last >> 32));
+                    }
+                  } else {
+                    list[cnt++] = ((uint64_t)hd << 32) | key;
+                  }
+                  Te = fmaxf(T, Tg);
+                }
+                if (!kRegList) {  // warp-uniform: compact every buffer that just filled
+                  uint32_t fm = __ballot_sync(0xFFFFFFFFu, cnt == p.lcap);
+                  while (fm) {
+                    const int src = __ffs((int)fm) - 1;
+                    fm &= fm - 1;
+                    uint64_t* buf = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, reinterpret_cast<unsigned long long>(list), src));
+                    const uint64_t kth = gt4_warp_compact(buf, p.lcap, p.k);
+                    if ((int)lane == src) {
+                      cnt = p.k;
+                      atomicMin(gq, (uint32_t)(kth >> 32));
+                      T = (float)(popq - (int)(uint32_t)(kth >> 32));
+                      Te = fmaxf(T, Tg);
+                    }
+                  }
+                }
+              }
+            }
+            HB_DIAG_ADD(dg_ins);
+          }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(bTEmpty + 8 * acc);
+        HB_TRACE(tcount, 6 + warp);
+      }
+      if (kRegList && live) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if ((uint32_t)i + p.k >= 16u) list[(uint32_t)i + p.k - 16u] = rl[i];
+      }
+    }
+#ifdef HB_GT_DIAG
+    if (warp == 0 && lane == 0) {
+      g_gt4_diag[blockIdx.x * 16 + 5] = dg_tfull;
+      g_gt4_diag[blockIdx.x * 16 + 6] = dg_ins;
+      g_gt4_diag[blockIdx.x * 16 + 7] = tcount;
+    }
+#endif
+  } else if (warp < kEpiWarps + kExpWarps) {
+    // ===================== expansion: packed bits -> E2M1 operands in shared memory =====================
+    const uint32_t ew = warp - kEpiWarps;
+    const uint32_t et = ew * 32 + lane;  // 0..255: row of the data tile
+    uint32_t stage = 0, sphase = 0, it = 0;
+    [[maybe_unused]] long long dg_empty = 0, dg_fence = 0, dg_afree = 0;
+    [[maybe_unused]] uint32_t xt = 0;
+    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+      const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
+      const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
+      // prefetch the first data tile's row while the query tile is written
+      uint64_t cur[16], nxt[16];
+      {
+        const uint64_t r = (uint64_t)t0 * kTileN + et;
+        if (et < (uint32_t)kTileN && r < p.n) {
+          const uint64_t* src = p.data + r * 16;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
+                         : "=l"(cur[4 * j]), "=l"(cur[4 * j + 1]), "=l"(cur[4 * j + 2]), "=l"(cur[4 * j + 3])
+                         : "l"(src + 4 * j));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) cur[j] = 0;
+        }
+      }
+      // ---- A: the query tile.  Word c of a K-block's eight fills 16-byte chunk c; output word u of the chunk holds,
+      // in nibble j, the element for bit 4j + u of the word: +-2, +-1, +-0.5, +-0.5 (sign bit = nibble bit 3, set when the
+      // query bit is clear), matching the data scales 0.5, 1, 2, 2 below ----
+      {
+        HB_DIAG_T0();
+        mbar_wait(bAFree, (it & 1) ^ 1);
+        HB_DIAG_ADD(dg_afree);
+      }
+      {
+        const uint32_t arow = et >> 1, kb0 = (et & 1) * 2;
+        const uint32_t q = qtile * kTileM + arow;
+        const bool live = q < p.nq;
+        const uint4* qp = reinterpret_cast<const uint4*>(p.queries + (size_t)(live ? q : 0) * 16);
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+          const uint32_t kb = kb0 + kk;
+          const uint4 qa = __ldg(qp + 2 * kb), qb = __ldg(qp + 2 * kb + 1);
+          const uint32_t w[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+          const uint32_t rowaddr = sA + kb * kAKBlockBytes + arow * 128;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint32_t o[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const uint32_t mag = (u == 0) ? 0x44444444u : (u == 1) ? 0x22222222u : 0x11111111u;
+              const uint32_t clr = ((w[c] >> u) & 0x11111111u) ^ 0x11111111u;
+              o[u] = live ? (mag | (clr << 3)) : 0u;
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + (((uint32_t)c ^ (arow & 7u)) << 4)), "r"(o[0]), "r"(o[1]),
+                         "r"(o[2]), "r"(o[3])
+                         : "memory");
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bAFull);
+      }
+      // ---- B: data tiles ----
+      // The next tile's row is fetched at the top of the tile (four 256-bit loads).  Every stage's proxy fence is a
+      // MEMBAR that waits for outstanding loads, so the load latency is exposed once per tile, overlapped with the
+      // wait for the first free stage.
+      for (uint32_t t = t0; t < t1; ++t) {
+        const uint64_t rn = (uint64_t)(t + 1) * kTileN + et;
+        if (t + 1 < t1 && et < (uint32_t)kTileN && rn < p.n) {
+          const uint64_t* src = p.data + rn * 16;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
+                         : "=l"(nxt[4 * j]), "=l"(nxt[4 * j + 1]), "=l"(nxt[4 * j + 2]), "=l"(nxt[4 * j + 3])
+                         : "l"(src + 4 * j));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) nxt[j] = 0;
+        }
+#pragma unroll
+        for (int kb = 0; kb < kKBlocks; ++kb) {
+          {
+            HB_DIAG_T0();
+            mbar_wait(bEmpty + 8 * stage, sphase ^ 1);
+            HB_DIAG_ADD(dg_empty);
+          }
+          const uint32_t rowaddr = sB + stage * kStageBytes + et * 128;
+          if (et < (uint32_t)kTileN) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {  // E2M1 codes 0001 = 0.5, 0010 = 1, 0100 = 2; bit 3 of each nibble reuses 2
+              const uint32_t w = (uint32_t)(cur[4 * kb + (c >> 1)] >> (32 * (c & 1)));
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + (((uint32_t)c ^ (et & 7u)) << 4)), "r"(w & 0x11111111u),
+                           "r"(w & 0x22222222u), "r"(w & 0x44444444u), "r"((w >> 1) & 0x44444444u)
+                           : "memory");
+            }
+          }
+          {
+            HB_DIAG_T0();
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            HB_DIAG_ADD(dg_fence);
+          }
+          if (lane == 0) mbar_arrive(bFull + 8 * stage);
+          if (ew == 0) HB_TRACE(xt, 10 + kb);
+          if (++stage == kStages) {
+            stage = 0;
+            sphase ^= 1;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) cur[j] = nxt[j];
+#ifdef HB_GT_DIAG
+        ++xt;
+#endif
+      }
+    }
+#ifdef HB_GT_DIAG
+    if (ew == 0 && lane == 0) {
+      g_gt4_diag[blockIdx.x * 16 + 3] = dg_empty;
+      g_gt4_diag[blockIdx.x * 16 + 4] = dg_fence;
+      g_gt4_diag[blockIdx.x * 16 + 8] = dg_afree;
+    }
+#endif
+  } else {
+    // ===================== MMA issue: one elected thread =====================
+    uint32_t stage = 0, sphase = 0, tcount = 0, it = 0;
+    [[maybe_unused]] long long dg_tempty = 0, dg_full = 0;
+    [[maybe_unused]] const long long dg_start = clock64();
+    const uint64_t da0 = umma_desc(sA), db0 = umma_desc(sB);
+    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+      const uint32_t chunk = item / p.n_qtiles;
+      const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
+      mbar_wait(bAFull, it & 1);
+      for (uint32_t t = t0; t < t1; ++t, ++tcount) {
+        const uint32_t acc = tcount & 1, ause = tcount >> 1;
+        {
+          HB_DIAG_T0();
+          mbar_wait(bTEmpty + 8 * acc, (ause & 1) ^ 1);
+          HB_DIAG_ADD(dg_tempty);
+        }
+        HB_TRACE(tcount, 0);
+        const uint32_t tmem_d = tmem + acc * kAccStride;
+#pragma unroll
+        for (int kb = 0; kb < kKBlocks; ++kb) {
+          {
+            HB_DIAG_T0();
+            mbar_wait(bFull + 8 * stage, sphase);
+            HB_DIAG_ADD(dg_full);
+          }
+          HB_TRACE(tcount, 18 + kb);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          if (elect_one_sync()) {
+            const uint64_t da = da0 + (uint64_t)(kb * (kAKBlockBytes >> 4)), db = db0 + (uint64_t)(stage * (kStageBytes >> 4));
+#pragma unroll
+            for (int j = 0; j < 4; ++j)  // K = 64 E2M1 per instruction: +32 B inside the swizzle atom = +2 in the encoded address
+              umma_mxf4(tmem_d, da + 2 * j, db + 2 * j, tmem + kSfCol, (kb | j) != 0);
+            umma_commit(bEmpty + 8 * stage);
+            if (kb == kKBlocks - 1) {
+              umma_commit(bTFull + 8 * acc);
+              if (t == t1 - 1) umma_commit(bAFree);
+            }
+          }
+          __syncwarp();
+          if (kb == kKBlocks - 1) HB_TRACE(tcount, 1);
+          if (++stage == kStages) {
+            stage = 0;
+            sphase ^= 1;
+          }
+        }
+      }
+    }
+#ifdef HB_GT_DIAG
+    if (lane == 0) {
+      g_gt4_diag[blockIdx.x * 16 + 0] = clock64() - dg_start;
+      g_gt4_diag[blockIdx.x * 16 + 1] = dg_tempty;
+      g_gt4_diag[blockIdx.x * 16 + 2] = dg_full;
+    }
+#endif
+  }
+
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+  }
+}
+
+}  // namespace
+
+#ifdef HB_GT_DIAG
+extern "C" int hb_debug_gt4_diag(long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, g_gt4_diag, sizeof(long long) * 256 * 16);
+}
+#endif
+
+bool ground_truth_mxf4_supported(const void* d_data, const void* d_queries, uint64_t n, uint64_t nq, uint32_t k) {
+  return n >= 1 && nq >= 1 && k >= 1 && k <= 1024 && (reinterpret_cast<uintptr_t>(d_data) & 31) == 0 &&
+         (reinterpret_cast<uintptr_t>(d_queries) & 15) == 0 && n <= 0xFFFFFFFFull - kTileN;
+}
+
+void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
+                             void* d_packed, cudaStream_t stream) {
+  HB_REQUIRE(ground_truth_mxf4_supported(d_data, d_queries, n, nq, k), HB_ERR_UNSUPPORTED,
+             "tcgen05 ground truth: needs 32-byte aligned data, 1 <= k <= 1024");
+  HB_REQUIRE(key_offset + n <= 0xFFFFFFFFull, HB_ERR_UNSUPPORTED, "keys must stay below 2^32");
+  HB_REQUIRE(nq <= 0x7FFFFF00ull, HB_ERR_UNSUPPORTED, "too many queries in one call");
+  int dev = 0, sms = 0;
+  HB_CUDA(cudaGetDevice(&dev));
+  HB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  GtParams p{};
+  p.data = static_cast<const uint64_t*>(d_data);
+  p.queries = static_cast<const uint64_t*>(d_queries);
+  p.n = n;
+  p.key_offset = key_offset;
+  p.nq = (uint32_t)nq;
+  p.k = k;
+  p.n_qtiles = (uint32_t)((nq + kTileM - 1) / kTileM);
+  p.n_tiles = (uint32_t)((n + kTileN - 1) / kTileN);
+  // chunks of data tiles: enough items to fill the grid several times over, picked so the last wave is nearly full
+  uint32_t best_chunks = 1;
+  double best_eff = -1.0;
+  const uint32_t max_chunks = std::min<uint32_t>(p.n_tiles, 96);
+  for (uint32_t c = 1; c <= max_chunks; ++c) {
+    const uint32_t tpc = (p.n_tiles + c - 1) / c;
+    const uint32_t chunks = (p.n_tiles + tpc - 1) / tpc;
+    const uint64_t items = (uint64_t)chunks * p.n_qtiles;
+    const uint64_t waves = (items + sms - 1) / sms;
+    // cost model: waves x (tiles per chunk + per-item overhead: writing the query tile and refilling the item's lists,
+    // in tile times -- register lists (k <= 16) refill in ~25, lists in global memory in ~4 per entry)
+    const double overhead = 4.0 + (k <= 16 ? 50.0 : 0.5 * k);
+    const double cost = (double)waves * (tpc + overhead);
+    const double eff = ((double)p.n_tiles * p.n_qtiles / sms) / cost;
+    if (eff > best_eff + 1e-9) {
+      best_eff = eff;
+      best_chunks = chunks;
+    }
+  }
+  p.n_chunks = best_chunks;
+  p.tiles_per_chunk = (p.n_tiles + p.n_chunks - 1) / p.n_chunks;
+  p.n_chunks = (p.n_tiles + p.tiles_per_chunk - 1) / p.tiles_per_chunk;
+
+  uint64_t* partial = nullptr;
+  p.lcap = k <= 16 ? k : 2 * k;
+  const size_t list_bytes = (size_t)p.n_chunks * nq * p.lcap * 8;
+  HB_CUDA(cudaMallocAsync(&partial, list_bytes + nq * 4, stream));
+  p.partial = partial;
+  p.gthr = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(partial) + list_bytes);
+  HB_CUDA(cudaMemsetAsync(p.gthr, 0xFF, nq * 4, stream));
+  const uint32_t n_items = p.n_qtiles * p.n_chunks;
+  const uint32_t grid = std::min<uint32_t>(n_items, (uint32_t)sms);
+  if (k <= 16) {
+    HB_CUDA(cudaFuncSetAttribute(gt_mxf4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    gt_mxf4_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(p);
+  } else {
+    HB_CUDA(cudaFuncSetAttribute(gt_mxf4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    gt_mxf4_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(p);
+  }
+  count_launches();
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) {
+    try {
+      topk_merge_device(partial, p.n_chunks, nq, k, d_packed, stream, /*sorted=*/k <= 16, p.lcap);
+    } catch (...) {
+      cudaFreeAsync(partial, stream);
+      throw;
+    }
+  }
+  cudaFreeAsync(partial, stream);
+  HB_CUDA(e);
+}
+
+}  // namespace hb

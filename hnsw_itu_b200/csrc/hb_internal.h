@@ -128,6 +128,10 @@ void ground_truth_scan_device(const void* d_data, uint64_t n, uint64_t key_offse
 bool ground_truth_mma_supported(const void* d_data, const void* d_queries, uint64_t n, uint64_t nq, uint32_t k);
 void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
                              void* d_packed, cudaStream_t stream);
+// the same GEMM with E2M1 operands (tcgen05.mma kind::mxf4.block_scale, unit scales); gt_mxf4.cu
+bool ground_truth_mxf4_supported(const void* d_data, const void* d_queries, uint64_t n, uint64_t nq, uint32_t k);
+void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
+                             void* d_packed, cudaStream_t stream);
 void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream,
                        bool sorted = true, uint32_t width = 0);  // !sorted: lists of `width` (default k) slots in any order, kNone = none
 void unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists, cudaStream_t stream);

@@ -196,7 +196,7 @@ def index_from_parts(algo: str, graphs: list[dict], ep: int | None, device: int 
     return Index(h.value)
 
 
-GT_ALGOS = {"auto": 0, "scan": 1, "mma": 2}  # hb_gt_algo
+GT_ALGOS = {"auto": 0, "scan": 1, "mma": 2, "mxf4": 3}  # hb_gt_algo
 
 
 def ground_truth(data, queries, k: int, device: int = 0, algo: str = "auto"):

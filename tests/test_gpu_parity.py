@@ -156,7 +156,7 @@ def test_ground_truth_parity(hb, oracle):
         q = oracle.synth(nq, 62, p)
         ok, od = oracle.ground_truth(data, q, k)
         m = min(n, k)
-        for algo in ("auto", "scan", "mma"):
+        for algo in ("auto", "scan", "mma", "mxf4"):
             gk, gd = hb.ground_truth(data, q, k, algo=algo)
             assert np.array_equal(gk[:, :m], ok[:, :m]) and np.array_equal(gd[:, :m], od[:, :m]), (dp, n, nq, k, algo)
             if n < k:
@@ -179,8 +179,9 @@ def test_ground_truth_parity(hb, oracle):
     (64, 70000, 128, 1),      # k = 1; more items than SMs' worth of chunks
     (1024, 513, 257, 1024),   # k > rows in most chunks, k at the supported maximum
 ])
-def test_ground_truth_tcgen05_vs_oracle(hb, oracle, dp, n, nq, k):
-    """The tcgen05 int8-GEMM formulation (gt_tcgen05.cu) against Bruteforce::search + sort restated by the oracle,
+@pytest.mark.parametrize("algo", ["mma", "mxf4"])
+def test_ground_truth_tcgen05_vs_oracle(hb, oracle, dp, n, nq, k, algo):
+    """The tcgen05 GEMM formulations (int8: gt_tcgen05.cu, E2M1: gt_mxf4.cu) against Bruteforce::search + sort restated by the oracle,
     and against the XOR+POPC scan kernel: ids and distances identical, including the (distance, key) tie order."""
     from oracle import oracle as orc
     p = orc.SynthParams(latent_dim=8, n_clusters=16, distinct_planes=dp)
@@ -189,7 +190,7 @@ def test_ground_truth_tcgen05_vs_oracle(hb, oracle, dp, n, nq, k):
     q[0] = data[n // 2]            # a query that is a member: distance 0
     if nq > 1:
         q[-1] = ~data[n - 1]       # and the complement of the last row: distance 1024 to it
-    mk, md = hb.ground_truth(data, q, k, algo="mma")
+    mk, md = hb.ground_truth(data, q, k, algo=algo)
     sk, sd = hb.ground_truth(data, q, k, algo="scan")
     assert np.array_equal(mk, sk) and np.array_equal(md, sd)
     ok, od = oracle.ground_truth(data, q, k)
@@ -198,9 +199,10 @@ def test_ground_truth_tcgen05_vs_oracle(hb, oracle, dp, n, nq, k):
     assert md[0, 0] == 0 and mk[0, 0] <= n // 2
 
 
-def test_ground_truth_tcgen05_all_bit_positions(hb):
+@pytest.mark.parametrize("algo", ["mma", "mxf4"])
+def test_ground_truth_tcgen05_all_bit_positions(hb, algo):
     """Every one of the 1024 bit positions contributes exactly 1 to the distance (the operand scaling/permutation
-    of the int8 expansion is position dependent): rows = one-hot sketches against the zero query and its complement."""
+    of the int8 / E2M1 expansion is position dependent): rows = one-hot sketches against the zero query and its complement."""
     data = np.zeros((1024 + 300, 16), dtype=np.uint64)
     for b in range(1024):
         data[b, b // 64] = np.uint64(1) << np.uint64(b % 64)
@@ -213,7 +215,7 @@ def test_ground_truth_tcgen05_all_bit_positions(hb):
     q[1] = ~q[1]
     for i in range(2, 40):
         q[i] = data[(i * 37) % 1024] | data[(i * 91 + 5) % 1024]
-    mk, md = hb.ground_truth(data, q, 50, algo="mma")
+    mk, md = hb.ground_truth(data, q, 50, algo=algo)
     sk, sd = hb.ground_truth(data, q, 50, algo="scan")
     assert np.array_equal(mk, sk) and np.array_equal(md, sd)
     assert (md[0, :50] == 1).all() and np.array_equal(mk[0, :50], np.arange(50, dtype=np.uint64))

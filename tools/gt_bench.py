@@ -12,7 +12,7 @@ NQ = int(sys.argv[2]) if len(sys.argv) > 2 else 10_000
 K = int(sys.argv[3]) if len(sys.argv) > 3 else 10
 REPS = int(sys.argv[4]) if len(sys.argv) > 4 else 3
 ALGOS = (sys.argv[5] if len(sys.argv) > 5 else "mma,scan").split(",")
-CODE = {"auto": 0, "scan": 1, "mma": 2}
+CODE = {"auto": 0, "scan": 1, "mma": 2, "mxf4": 3}
 
 import hnsw_itu_b200 as hb
 L = _lib.lib()
