@@ -195,7 +195,7 @@ void ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, co
                          void* d_packed, cudaStream_t stream, int algo) {
   HB_REQUIRE(algo == HB_GT_AUTO || algo == HB_GT_SCAN || algo == HB_GT_MMA || algo == HB_GT_MXF4, HB_ERR_INVALID, "unknown ground-truth algorithm");
   if (algo == HB_GT_AUTO)
-    algo = (nq >= 32 && n >= 4096 && ground_truth_mma_supported(d_data, d_queries, n, nq, k)) ? HB_GT_MMA : HB_GT_SCAN;
+    algo = (nq >= 32 && n >= 4096 && ground_truth_mxf4_supported(d_data, d_queries, n, nq, k)) ? HB_GT_MXF4 : HB_GT_SCAN;
   if (algo == HB_GT_MXF4)
     ground_truth_mxf4_device(d_data, n, key_offset, d_queries, nq, k, d_packed, stream);
   else if (algo == HB_GT_MMA)

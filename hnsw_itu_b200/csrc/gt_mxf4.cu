@@ -379,22 +379,42 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
     for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
-      // prefetch the first data tile's row while the query tile is written
-      uint64_t cur[16], nxt[16];
-      {
-        const uint64_t r = (uint64_t)t0 * kTileN + et;
-        if (et < (uint32_t)kTileN && r < p.n) {
-          const uint64_t* src = p.data + r * 16;
+      // Coalesced tile loads: the warp's 32 rows go in four 256-bit load instructions of 8 rows x 128 B each (8 full
+      // lines per instruction instead of 32 quarter lines).  In instruction j lane (r4, m8) = (lane >> 3, lane & 7)
+      // fetches the 32-byte K-block (r4 + j) & 3 of row 8j + m8, so over j it holds all four K-blocks -- of four
+      // different rows.  rotate() then orders them by K-block: set kb = K-block kb of row 8((kb - r4) & 3) + m8, which is
+      // the row this thread writes in stage kb.  Eight consecutive lanes write eight consecutive rows: conflict-free.
+      const uint32_t r4 = lane >> 3, m8 = lane & 7;
+      auto load_tile = [&](uint32_t t, bool in_range, uint64_t(&R)[16]) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t lrow = ew * 32 + 8 * j + m8;
+          const uint64_t grow = (uint64_t)t * kTileN + lrow;
+          if (in_range && lrow < (uint32_t)kTileN && grow < p.n) {
             asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
-                         : "=l"(cur[4 * j]), "=l"(cur[4 * j + 1]), "=l"(cur[4 * j + 2]), "=l"(cur[4 * j + 3])
-                         : "l"(src + 4 * j));
-        } else {
+                         : "=l"(R[4 * j]), "=l"(R[4 * j + 1]), "=l"(R[4 * j + 2]), "=l"(R[4 * j + 3])
+                         : "l"(p.data + grow * 16 + ((r4 + j) & 3u) * 4));
+          } else {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) cur[j] = 0;
+            for (int e = 0; e < 4; ++e) R[4 * j + e] = 0;
+          }
         }
-      }
+      };
+      auto rotate = [&](uint64_t(&R)[16]) {  // R[kb] <- R[(kb - r4) & 3], as two conditional rotations with static indices
+        const bool b0 = r4 & 1u, b1 = r4 & 2u;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const uint64_t a0 = R[e], a1 = R[4 + e], a2 = R[8 + e], a3 = R[12 + e];
+          const uint64_t c0 = b0 ? a3 : a0, c1 = b0 ? a0 : a1, c2 = b0 ? a1 : a2, c3 = b0 ? a2 : a3;
+          R[e] = b1 ? c2 : c0;
+          R[4 + e] = b1 ? c3 : c1;
+          R[8 + e] = b1 ? c0 : c2;
+          R[12 + e] = b1 ? c1 : c3;
+        }
+      };
+      // prefetch the first data tile while the query tile is written
+      uint64_t cur[16], nxt[16];
+      load_tile(t0, true, cur);
       // ---- A: the query tile.  Word c of a K-block's eight fills 16-byte chunk c; output word u of the chunk holds,
       // in nibble j, the element for bit 4j + u of the word: +-2, +-1, +-0.5, +-0.5 (sign bit = nibble bit 3, set when the
       // query bit is clear), matching the data scales 0.5, 1, 2, 2 below ----
@@ -433,22 +453,12 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
         if (lane == 0) mbar_arrive(bAFull);
       }
       // ---- B: data tiles ----
-      // The next tile's row is fetched at the top of the tile (four 256-bit loads).  Every stage's proxy fence is a
+      // The next tile's rows are fetched at the top of the tile (four 256-bit loads).  Every stage's proxy fence is a
       // MEMBAR that waits for outstanding loads, so the load latency is exposed once per tile, overlapped with the
       // wait for the first free stage.
       for (uint32_t t = t0; t < t1; ++t) {
-        const uint64_t rn = (uint64_t)(t + 1) * kTileN + et;
-        if (t + 1 < t1 && et < (uint32_t)kTileN && rn < p.n) {
-          const uint64_t* src = p.data + rn * 16;
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
-                         : "=l"(nxt[4 * j]), "=l"(nxt[4 * j + 1]), "=l"(nxt[4 * j + 2]), "=l"(nxt[4 * j + 3])
-                         : "l"(src + 4 * j));
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) nxt[j] = 0;
-        }
+        load_tile(t + 1, t + 1 < t1, nxt);
+        rotate(cur);
 #pragma unroll
         for (int kb = 0; kb < kKBlocks; ++kb) {
           {
@@ -456,15 +466,14 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
             mbar_wait(bEmpty + 8 * stage, sphase ^ 1);
             HB_DIAG_ADD(dg_empty);
           }
-          const uint32_t rowaddr = sB + stage * kStageBytes + et * 128;
-          if (et < (uint32_t)kTileN) {
+          // rows 240..255 of the stage exist but are never read: the last warp's zero rows may land there
+          const uint32_t rowaddr = sB + stage * kStageBytes + (ew * 32 + 8 * (((uint32_t)kb - r4) & 3u) + m8) * 128;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {  // E2M1 codes 0001 = 0.5, 0010 = 1, 0100 = 2; bit 3 of each nibble reuses 2
-              const uint32_t w = (uint32_t)(cur[4 * kb + (c >> 1)] >> (32 * (c & 1)));
-              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + (((uint32_t)c ^ (et & 7u)) << 4)), "r"(w & 0x11111111u),
-                           "r"(w & 0x22222222u), "r"(w & 0x44444444u), "r"((w >> 1) & 0x44444444u)
-                           : "memory");
-            }
+          for (int c = 0; c < 8; ++c) {  // E2M1 codes 0001 = 0.5, 0010 = 1, 0100 = 2; bit 3 of each nibble reuses 2
+            const uint32_t w = (uint32_t)(cur[4 * kb + (c >> 1)] >> (32 * (c & 1)));
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + (((uint32_t)c ^ m8) << 4)), "r"(w & 0x11111111u),
+                         "r"(w & 0x22222222u), "r"(w & 0x44444444u), "r"((w >> 1) & 0x44444444u)
+                         : "memory");
           }
           {
             HB_DIAG_T0();

@@ -1,5 +1,5 @@
 """Phase clocks of the tcgen05 ground-truth kernel from a -DHB_GT_DIAG build (diagnostics, not the product):
-   tools/ab_build.sh gtdiag "-DHB_GT_DIAG" && HB_LIB_PATH=variants/gtdiag.so python tools/gt_diag.py [N] [NQ] [K]"""
+   tools/ab_build.sh gtdiag "-DHB_GT_DIAG" && HB_LIB_PATH=variants/gtdiag.so python tools/gt_diag.py [N] [NQ] [K] [mma|mxf4]"""
 import ctypes as C, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -9,6 +9,7 @@ from hnsw_itu_b200 import _lib
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
 NQ = int(sys.argv[2]) if len(sys.argv) > 2 else 10_000
 K = int(sys.argv[3]) if len(sys.argv) > 3 else 10
+ALGO = sys.argv[4] if len(sys.argv) > 4 else "mma"   # "mma" (gt_tcgen05.cu) or "mxf4" (gt_mxf4.cu)
 L = _lib.lib()
 d = torch.empty((N, 16), dtype=torch.int64, device="cuda"); q = torch.empty((NQ, 16), dtype=torch.int64, device="cuda")
 hb.synth_sketches(d.data_ptr(), N, 1003); hb.synth_sketches(q.data_ptr(), NQ, 1004)
@@ -16,11 +17,11 @@ out = torch.empty((NQ, K), dtype=torch.int64, device="cuda")
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 for _ in range(2):
     e0.record()
-    _lib.check(L.hb_ground_truth_device_algo(d.data_ptr(), N, 0, q.data_ptr(), NQ, K, 2, out.data_ptr(), None))
+    _lib.check(L.hb_ground_truth_device_algo(d.data_ptr(), N, 0, q.data_ptr(), NQ, K, {"mma": 2, "mxf4": 3}[ALGO], out.data_ptr(), None))
     e1.record(); torch.cuda.synchronize()
 print("ms", e0.elapsed_time(e1))
 buf = np.zeros(256 * 16, dtype=np.int64)
-assert L.hb_debug_gt_diag(buf.ctypes.data_as(C.c_void_p)) == 0
+assert getattr(L, "hb_debug_gt_diag" if ALGO == "mma" else "hb_debug_gt4_diag")(buf.ctypes.data_as(C.c_void_p)) == 0
 g = buf.reshape(256, 16)[:148]
 names = ["kernel", "mma:wait_acc_free", "mma:wait_stage_full", "exp:wait_stage_empty", "exp:fence", "epi:wait_acc_full", "epi:insert", "tiles", "exp:wait_A_free"]
 tiles = g[:, 7].astype(float)
