@@ -15,6 +15,10 @@
 
 #include "hb_internal.h"
 
+#ifndef HB_GT_PROBE_MMAS
+#define HB_GT_PROBE_MMAS 4
+#endif
+
 namespace hb {
 namespace {
 
@@ -190,7 +194,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(bFull + 8 * s, kExpWarps);
+      mbar_init(bFull + 8 * s, kExpWarps / 2);
       mbar_init(bEmpty + 8 * s, 1);
     }
     for (int a = 0; a < 2; ++a) {
@@ -224,6 +228,12 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
   const uint32_t n_items = p.n_qtiles * p.n_chunks;
+#if defined(HB_GT_PROBE_STS) && HB_GT_PROBE_STS < 8
+  for (uint32_t i = threadIdx.x; i < kStages * kStageBytes / 16; i += blockDim.x)
+    asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(sB + i * 16), "r"(0u) : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+#endif
 
   if (warp < kEpiWarps) {
     // ===================== epilogue: thread = one query row of the accumulator =====================
@@ -372,44 +382,46 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
   } else if (warp < kEpiWarps + kExpWarps) {
     // ===================== expansion: packed bits -> E2M1 operands in shared memory =====================
     const uint32_t ew = warp - kEpiWarps;
-    const uint32_t et = ew * 32 + lane;  // 0..255: row of the data tile
-    uint32_t stage = 0, sphase = 0, it = 0;
-    [[maybe_unused]] long long dg_empty = 0, dg_fence = 0, dg_afree = 0;
+    const uint32_t et = ew * 32 + lane;  // 0..255: thread of the expansion role (the query-tile fill is indexed by it)
+    const uint32_t grp = ew & 1u, wi = ew >> 1;
+    uint32_t stage = 2 * grp, sphase = 0, it = 0;
+    [[maybe_unused]] long long dg_empty = 0, dg_fence = 0, dg_afree = 0, dg_top = 0, dg_sts = 0, dg_mov = 0;
     [[maybe_unused]] uint32_t xt = 0;
     for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
-      // Coalesced tile loads: the warp's 32 rows go in four 256-bit load instructions of 8 rows x 128 B each (8 full
-      // lines per instruction instead of 32 quarter lines).  In instruction j lane (r4, m8) = (lane >> 3, lane & 7)
-      // fetches the 32-byte K-block (r4 + j) & 3 of row 8j + m8, so over j it holds all four K-blocks -- of four
-      // different rows.  rotate() then orders them by K-block: set kb = K-block kb of row 8((kb - r4) & 3) + m8, which is
-      // the row this thread writes in stage kb.  Eight consecutive lanes write eight consecutive rows: conflict-free.
-      const uint32_t r4 = lane >> 3, m8 = lane & 7;
+      // Two groups of four warps fill alternate pairs of stages: group 0 the K-blocks 0,1 of every tile, group 1 the
+      // K-blocks 2,3.  A stage costs a burst of stores and then a proxy fence that blocks the warp for a few hundred
+      // cycles; with all eight warps in lockstep the store pipe idled during every fence, with two groups one stores
+      // while the other fences.  A warp covers 64 rows (8 octets); in load instruction j the lane (r2, x, m8) fetches the
+      // 32-byte K-block 2 grp + ((x + j) & 1) of row 8 (2j + r2) + m8: lanes x = 0, 1 take the two halves of the same
+      // 64 bytes (16 half lines per instruction), and order() swaps so that R[0..3], R[8..11] hold the group's first
+      // K-block (of the rows in octets 2x + r2 and 4 + 2x + r2) and R[4..7], R[12..15] the second (octets 2(1-x) + r2,
+      // 4 + 2(1-x) + r2).  Eight consecutive lanes always store eight consecutive rows: conflict-free.
+      const uint32_t m8 = lane & 7, x = (lane >> 3) & 1u, r2 = lane >> 4;
       auto load_tile = [&](uint32_t t, bool in_range, uint64_t(&R)[16]) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const uint32_t lrow = ew * 32 + 8 * j + m8;
+          const uint32_t lrow = 64 * wi + 8 * (2 * j + r2) + m8;
           const uint64_t grow = (uint64_t)t * kTileN + lrow;
           if (in_range && lrow < (uint32_t)kTileN && grow < p.n) {
             asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
                          : "=l"(R[4 * j]), "=l"(R[4 * j + 1]), "=l"(R[4 * j + 2]), "=l"(R[4 * j + 3])
-                         : "l"(p.data + grow * 16 + ((r4 + j) & 3u) * 4));
+                         : "l"(p.data + grow * 16 + (2 * grp + ((x + j) & 1u)) * 4));
           } else {
 #pragma unroll
             for (int e = 0; e < 4; ++e) R[4 * j + e] = 0;
           }
         }
       };
-      auto rotate = [&](uint64_t(&R)[16]) {  // R[kb] <- R[(kb - r4) & 3], as two conditional rotations with static indices
-        const bool b0 = r4 & 1u, b1 = r4 & 2u;
+      auto order = [&](uint64_t(&R)[16]) {
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const uint64_t a0 = R[e], a1 = R[4 + e], a2 = R[8 + e], a3 = R[12 + e];
-          const uint64_t c0 = b0 ? a3 : a0, c1 = b0 ? a0 : a1, c2 = b0 ? a1 : a2, c3 = b0 ? a2 : a3;
-          R[e] = b1 ? c2 : c0;
-          R[4 + e] = b1 ? c3 : c1;
-          R[8 + e] = b1 ? c0 : c2;
-          R[12 + e] = b1 ? c1 : c3;
+          R[e] = x ? a1 : a0;
+          R[4 + e] = x ? a0 : a1;
+          R[8 + e] = x ? a3 : a2;
+          R[12 + e] = x ? a2 : a3;
         }
       };
       // prefetch the first data tile while the query tile is written
@@ -457,24 +469,47 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
       // MEMBAR that waits for outstanding loads, so the load latency is exposed once per tile, overlapped with the
       // wait for the first free stage.
       for (uint32_t t = t0; t < t1; ++t) {
-        load_tile(t + 1, t + 1 < t1, nxt);
-        rotate(cur);
+        {
+          HB_DIAG_T0();
+          #ifdef HB_GT_PROBE_NOLDG
+          load_tile(t + 1, false, nxt);
+#else
+          load_tile(t + 1, t + 1 < t1, nxt);
+#endif
+          order(cur);
+          HB_DIAG_ADD(dg_top);
+        }
 #pragma unroll
-        for (int kb = 0; kb < kKBlocks; ++kb) {
+        for (int sg = 0; sg < 2; ++sg) {
+          [[maybe_unused]] const uint32_t kb = 2 * grp + sg;
           {
             HB_DIAG_T0();
             mbar_wait(bEmpty + 8 * stage, sphase ^ 1);
             HB_DIAG_ADD(dg_empty);
           }
-          // rows 240..255 of the stage exist but are never read: the last warp's zero rows may land there
-          const uint32_t rowaddr = sB + stage * kStageBytes + (ew * 32 + 8 * (((uint32_t)kb - r4) & 3u) + m8) * 128;
+          // rows 240..255 of the stage exist but are never read: the last warp's zero rows land there
+          const uint32_t oct = (sg == 0 ? 2 * x : 2 * (1 - x)) + r2;
+          [[maybe_unused]] const long long dg_s0 = clock64();
+#ifndef HB_GT_PROBE_STS
+#define HB_GT_PROBE_STS 8  // probe builds (wrong results): fewer stores or fewer MMAs, to time the other side alone
+#endif
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {  // E2M1 codes 0001 = 0.5, 0010 = 1, 0100 = 2; bit 3 of each nibble reuses 2
-            const uint32_t w = (uint32_t)(cur[4 * kb + (c >> 1)] >> (32 * (c & 1)));
-            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + (((uint32_t)c ^ m8) << 4)), "r"(w & 0x11111111u),
-                         "r"(w & 0x22222222u), "r"(w & 0x44444444u), "r"((w >> 1) & 0x44444444u)
-                         : "memory");
+          for (int h = 0; h < 2; ++h) {
+            const uint32_t rowaddr = sB + stage * kStageBytes + (64 * wi + 8 * (oct + 4 * h) + m8) * 128;
+#pragma unroll
+            for (int c = 0; c < HB_GT_PROBE_STS; ++c) {  // E2M1 codes 0001 = 0.5, 0010 = 1, 0100 = 2; bit 3 of each nibble reuses 2
+              const uint32_t w = (uint32_t)(cur[8 * h + 4 * sg + (c >> 1)] >> (32 * (c & 1)));
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + (((uint32_t)c ^ m8) << 4)), "r"(w & 0x11111111u),
+                           "r"(w & 0x22222222u), "r"(w & 0x44444444u), "r"((w >> 1) & 0x44444444u)
+                           : "memory");
+            }
           }
+#if HB_GT_PROBE_STS < 8
+          if (cur[4 * sg] == 0x123456789ull) asm volatile("st.shared.b32 [%0], %1;" ::"r"(sB + stage * kStageBytes), "r"((uint32_t)cur[4 * sg + 1] + (uint32_t)cur[4 * sg + 2] + (uint32_t)cur[4 * sg + 3] + (uint32_t)cur[8 + 4 * sg] + (uint32_t)cur[9 + 4 * sg]+ (uint32_t)cur[10 + 4 * sg]+ (uint32_t)cur[11 + 4 * sg]) : "memory");
+#endif
+#ifdef HB_GT_DIAG
+          dg_sts += clock64() - dg_s0;
+#endif
           {
             HB_DIAG_T0();
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -482,14 +517,26 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
             HB_DIAG_ADD(dg_fence);
           }
           if (lane == 0) mbar_arrive(bFull + 8 * stage);
-          if (ew == 0) HB_TRACE(xt, 10 + kb);
+          if (wi == 0) HB_TRACE(xt, 10 + kb);
           if (++stage == kStages) {
             stage = 0;
             sphase ^= 1;
           }
         }
+        stage += 2;  // the other group's pair
+        if (stage >= (uint32_t)kStages) {
+          stage -= kStages;
+          sphase ^= 1;
+        }
+        {
+          HB_DIAG_T0();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) cur[j] = nxt[j];
+          for (int j = 0; j < 16; ++j) cur[j] = nxt[j];
+#ifdef HB_GT_DIAG
+          if (cur[0] == 0x1234567ull && cur[5] == 0x77ull && cur[10] == 1 && cur[15] == 3) ++xt;  // make the clock wait for the loads
+#endif
+          HB_DIAG_ADD(dg_mov);
+        }
 #ifdef HB_GT_DIAG
         ++xt;
 #endif
@@ -500,6 +547,9 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
       g_gt4_diag[blockIdx.x * 16 + 3] = dg_empty;
       g_gt4_diag[blockIdx.x * 16 + 4] = dg_fence;
       g_gt4_diag[blockIdx.x * 16 + 8] = dg_afree;
+      g_gt4_diag[blockIdx.x * 16 + 9] = dg_top;
+      g_gt4_diag[blockIdx.x * 16 + 10] = dg_sts;
+      g_gt4_diag[blockIdx.x * 16 + 11] = dg_mov;
     }
 #endif
   } else {
@@ -533,7 +583,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
           if (elect_one_sync()) {
             const uint64_t da = da0 + (uint64_t)(kb * (kAKBlockBytes >> 4)), db = db0 + (uint64_t)(stage * (kStageBytes >> 4));
 #pragma unroll
-            for (int j = 0; j < 4; ++j)  // K = 64 E2M1 per instruction: +32 B inside the swizzle atom = +2 in the encoded address
+            for (int j = 0; j < HB_GT_PROBE_MMAS; ++j)  // K = 64 E2M1 per instruction: +32 B inside the swizzle atom = +2 in the encoded address
               umma_mxf4(tmem_d, da + 2 * j, db + 2 * j, tmem + kSfCol, (kb | j) != 0);
             umma_commit(bEmpty + 8 * stage);
             if (kb == kKBlocks - 1) {

@@ -16,7 +16,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -k 'regex:hnsw_search|
 echo "launch list rc=$?"
 ncu --set full --clock-control none --import-source on -k 'regex:hnsw_search' -s 4 -c 2 -f -o $out/search_$tag $cmd > $out/ncu_full_$tag.log 2>&1
 echo "full capture (search) rc=$?"
-gcmd="python tools/gt_bench.py 10000000 10000 10 1 mma"
-$gcmd > $out/gt_plain_$tag.json 2>&1 && ncu --set full --clock-control none --import-source on -k 'regex:gt_mma' -s 1 -c 1 -f -o $out/gt_$tag $gcmd > $out/ncu_gt_$tag.log 2>&1
+gcmd="python tools/gt_bench.py 10000000 10000 10 1 mxf4"
+$gcmd > $out/gt_plain_$tag.json 2>&1 && ncu --set full --clock-control none --import-source on -k 'regex:gt_mxf4' -s 1 -c 1 -f -o $out/gt_$tag $gcmd > $out/ncu_gt_$tag.log 2>&1
 echo "full capture (ground truth) rc=$?"
 ls -la $out
