@@ -26,16 +26,21 @@ constexpr uint64_t kNone = ~0ull;
 constexpr int kTileM = 128;   // queries per work item (UMMA M)
 constexpr int kTileN = 240;   // data rows per accumulator tile (UMMA N): 2 x 240 + 16 scale-factor columns <= 512
 constexpr int kGroup = 48;      // accumulator columns an epilogue thread reads per step (240 = 5 x 48)
-constexpr int kStageRows = 256; // rows a stage buffer holds (the last 16 are never written or read)
 constexpr uint32_t kAccStride = 256, kSfCol = 496;  // TMEM columns: accumulators at 0 and 256, scale factors at 496..511
 constexpr int kKBlocks = 4;   // 1024 bits = 4 K-blocks of 256 E2M1 (one 128-B swizzle atom row each)
-constexpr int kStages = 5;
+constexpr int kStages = 4;
 constexpr int kEpiWarps = 4, kExpWarps = 8;
-constexpr int kThreads = (kEpiWarps + kExpWarps + 1) * 32;
+constexpr int kThreads = (kEpiWarps + kExpWarps + 2) * 32;  // + the MMA warp + the loader warp
 constexpr uint32_t kABytes = kTileM * 512;            // 4 K-blocks x (128 rows x 128 B)
 constexpr uint32_t kAKBlockBytes = kTileM * 128;
-constexpr uint32_t kStageBytes = kStageRows * 128;
-constexpr uint32_t kBarOffset = kABytes + kStages * kStageBytes;
+constexpr uint32_t kStageBytes = kTileN * 128;
+// the packed rows of one data tile as the bulk copies deliver them (a few large copies: one 128-byte copy per row
+// at a conflict-free pitch was tried and costs ~54 cycles per copy, 13 k cycles per tile)
+constexpr uint32_t kRawPitch = 128, kRawBytes = kTileN * kRawPitch;
+constexpr uint32_t kCopyRows = 60;  // rows per bulk copy: four copies per tile
+constexpr uint32_t kRawOffset = kABytes + kStages * kStageBytes;
+constexpr uint32_t kBarOffset = kRawOffset + kRawBytes;
+static_assert(kStageBytes % 1024 == 0 && kRawOffset % 16 == 0 && kBarOffset % 8 == 0, "smem layout");
 constexpr uint32_t kSmemBytes = kBarOffset + 192 + 1024;  // + barriers + alignment slack
 
 // instruction descriptor (cute::UMMA::InstrDescriptorBlockScaled layout): A = B = E2M1 (MXF4 format 1), both K-major,
@@ -185,10 +190,10 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;  // swizzle atoms need 1024-B alignment
   unsigned char* sm = smem_raw + (base - raw);
-  const uint32_t sA = base, sB = base + kABytes, sBar = base + kBarOffset;
-  // barriers: full[5] empty[5] tfull[2] tempty[2] a_full a_free (128 bytes), then the TMEM base slot
+  const uint32_t sA = base, sB = base + kABytes, sRaw = base + kRawOffset, sBar = base + kBarOffset;
+  // barriers: full[4] empty[4] tfull[2] tempty[2] a_full a_free raw_full raw_free (112 bytes), then the TMEM base slot
   const uint32_t bFull = sBar, bEmpty = sBar + 8 * kStages, bTFull = sBar + 16 * kStages, bTEmpty = bTFull + 16, bAFull = bTEmpty + 16,
-                 bAFree = bAFull + 8;
+                 bAFree = bAFull + 8, bRawFull = bAFree + 8, bRawFree = bRawFull + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + kBarOffset + 128);
 
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -203,6 +208,8 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
     }
     mbar_init(bAFull, kExpWarps);
     mbar_init(bAFree, 1);
+    mbar_init(bRawFull, 1);
+    mbar_init(bRawFree, kExpWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -386,47 +393,10 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
     const uint32_t grp = ew & 1u, wi = ew >> 1;
     uint32_t stage = 2 * grp, sphase = 0, it = 0;
     [[maybe_unused]] long long dg_empty = 0, dg_fence = 0, dg_afree = 0, dg_top = 0, dg_sts = 0, dg_mov = 0;
-    [[maybe_unused]] uint32_t xt = 0;
+    uint32_t xt = 0;  // tiles so far: parity of the raw buffer
     for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
-      // Two groups of four warps fill alternate pairs of stages: group 0 the K-blocks 0,1 of every tile, group 1 the
-      // K-blocks 2,3.  A stage costs a burst of stores and then a proxy fence that blocks the warp for a few hundred
-      // cycles; with all eight warps in lockstep the store pipe idled during every fence, with two groups one stores
-      // while the other fences.  A warp covers 64 rows (8 octets); in load instruction j the lane (r2, x, m8) fetches the
-      // 32-byte K-block 2 grp + ((x + j) & 1) of row 8 (2j + r2) + m8: lanes x = 0, 1 take the two halves of the same
-      // 64 bytes (16 half lines per instruction), and order() swaps so that R[0..3], R[8..11] hold the group's first
-      // K-block (of the rows in octets 2x + r2 and 4 + 2x + r2) and R[4..7], R[12..15] the second (octets 2(1-x) + r2,
-      // 4 + 2(1-x) + r2).  Eight consecutive lanes always store eight consecutive rows: conflict-free.
-      const uint32_t m8 = lane & 7, x = (lane >> 3) & 1u, r2 = lane >> 4;
-      auto load_tile = [&](uint32_t t, bool in_range, uint64_t(&R)[16]) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const uint32_t lrow = 64 * wi + 8 * (2 * j + r2) + m8;
-          const uint64_t grow = (uint64_t)t * kTileN + lrow;
-          if (in_range && lrow < (uint32_t)kTileN && grow < p.n) {
-            asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
-                         : "=l"(R[4 * j]), "=l"(R[4 * j + 1]), "=l"(R[4 * j + 2]), "=l"(R[4 * j + 3])
-                         : "l"(p.data + grow * 16 + (2 * grp + ((x + j) & 1u)) * 4));
-          } else {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) R[4 * j + e] = 0;
-          }
-        }
-      };
-      auto order = [&](uint64_t(&R)[16]) {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const uint64_t a0 = R[e], a1 = R[4 + e], a2 = R[8 + e], a3 = R[12 + e];
-          R[e] = x ? a1 : a0;
-          R[4 + e] = x ? a0 : a1;
-          R[8 + e] = x ? a3 : a2;
-          R[12 + e] = x ? a2 : a3;
-        }
-      };
-      // prefetch the first data tile while the query tile is written
-      uint64_t cur[16], nxt[16];
-      load_tile(t0, true, cur);
       // ---- A: the query tile.  Word c of a K-block's eight fills 16-byte chunk c; output word u of the chunk holds,
       // in nibble j, the element for bit 4j + u of the word: +-2, +-1, +-0.5, +-0.5 (sign bit = nibble bit 3, set when the
       // query bit is clear), matching the data scales 0.5, 1, 2, 2 below ----
@@ -465,20 +435,50 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
         if (lane == 0) mbar_arrive(bAFull);
       }
       // ---- B: data tiles ----
-      // The next tile's rows are fetched at the top of the tile (four 256-bit loads).  Every stage's proxy fence is a
-      // MEMBAR that waits for outstanding loads, so the load latency is exposed once per tile, overlapped with the
-      // wait for the first free stage.
-      for (uint32_t t = t0; t < t1; ++t) {
+      // The loader warp's bulk copies put the tile's packed rows in the raw buffer; each thread takes the 64 bytes its
+      // group needs of two rows (64 wi + lane and 64 wi + 32 + lane) into registers and the buffer goes back to the
+      // loader as soon as the values are in registers.  Global loads issued by
+      // these warps would be waited for by that fence, a full memory latency per tile (28 -> 40 ms).
+      // Two groups of four warps fill alternate pairs of stages: group 0 the K-blocks 0,1 of every tile, group 1 the
+      // K-blocks 2,3, so one group stores while the other sits in its fence.  Eight consecutive lanes read and write
+      // eight consecutive rows: no bank conflicts on either side.
+      for (uint32_t t = t0; t < t1; ++t, ++xt) {
+        uint32_t cur[2][16];
         {
           HB_DIAG_T0();
-          #ifdef HB_GT_PROBE_NOLDG
-          load_tile(t + 1, false, nxt);
-#else
-          load_tile(t + 1, t + 1 < t1, nxt);
-#endif
-          order(cur);
+          mbar_wait(bRawFull, xt & 1);
           HB_DIAG_ADD(dg_top);
         }
+        // Rows are 128 B apart, so the same 16 bytes of eight consecutive rows share a bank group: lane l reads its
+        // four 16-byte pieces in the order (e + l) & 3 (two lanes per bank group, the floor for a 64-byte window) and
+        // two select stages put them back in order with static register indices.
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const uint32_t lrow = 64 * wi + 32 * h + lane;
+          const bool valid = lrow < (uint32_t)kTileN && (uint64_t)t * kTileN + lrow < p.n;
+          const uint32_t ra = sRaw + (valid ? lrow : 0u) * kRawPitch + grp * 64;
+          uint32_t tmp[16];
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(tmp[4 * e]), "=r"(tmp[4 * e + 1]), "=r"(tmp[4 * e + 2]), "=r"(tmp[4 * e + 3])
+                         : "r"(ra + 16 * (((uint32_t)e + lane) & 3u))
+                         : "memory");
+          const bool b0 = lane & 1u, b1 = lane & 2u;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {  // cur[4 j + i] = tmp[4 ((j - lane) & 3) + i]
+            const uint32_t a0 = tmp[i], a1 = tmp[4 + i], a2 = tmp[8 + i], a3 = tmp[12 + i];
+            const uint32_t c0 = b0 ? a3 : a0, c1 = b0 ? a0 : a1, c2 = b0 ? a1 : a2, c3 = b0 ? a2 : a3;
+            cur[h][i] = valid ? (b1 ? c2 : c0) : 0u;
+            cur[h][4 + i] = valid ? (b1 ? c3 : c1) : 0u;
+            cur[h][8 + i] = valid ? (b1 ? c0 : c2) : 0u;
+            cur[h][12 + i] = valid ? (b1 ? c1 : c3) : 0u;
+          }
+        }
+        // the selects consumed every loaded word, so the reads have been performed: hand the buffer back right away
+        // (the copy for the next tile then has this whole tile's expansion time to land)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bRawFree);
 #pragma unroll
         for (int sg = 0; sg < 2; ++sg) {
           [[maybe_unused]] const uint32_t kb = 2 * grp + sg;
@@ -487,26 +487,24 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
             mbar_wait(bEmpty + 8 * stage, sphase ^ 1);
             HB_DIAG_ADD(dg_empty);
           }
-          // rows 240..255 of the stage exist but are never read: the last warp's zero rows land there
-          const uint32_t oct = (sg == 0 ? 2 * x : 2 * (1 - x)) + r2;
           [[maybe_unused]] const long long dg_s0 = clock64();
 #ifndef HB_GT_PROBE_STS
 #define HB_GT_PROBE_STS 8  // probe builds (wrong results): fewer stores or fewer MMAs, to time the other side alone
 #endif
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
-            const uint32_t rowaddr = sB + stage * kStageBytes + (64 * wi + 8 * (oct + 4 * h) + m8) * 128;
+            const uint32_t lrow = 64 * wi + 32 * h + lane;
+            const uint32_t rowaddr = sB + stage * kStageBytes + lrow * 128;
+            if (lrow < (uint32_t)kTileN) {
 #pragma unroll
-            for (int c = 0; c < HB_GT_PROBE_STS; ++c) {  // E2M1 codes 0001 = 0.5, 0010 = 1, 0100 = 2; bit 3 of each nibble reuses 2
-              const uint32_t w = (uint32_t)(cur[8 * h + 4 * sg + (c >> 1)] >> (32 * (c & 1)));
-              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + (((uint32_t)c ^ m8) << 4)), "r"(w & 0x11111111u),
-                           "r"(w & 0x22222222u), "r"(w & 0x44444444u), "r"((w >> 1) & 0x44444444u)
-                           : "memory");
+              for (int c = 0; c < HB_GT_PROBE_STS; ++c) {  // E2M1 codes 0001 = 0.5, 0010 = 1, 0100 = 2; bit 3 of each nibble reuses 2
+                const uint32_t w = cur[h][8 * sg + c];
+                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + (((uint32_t)c ^ (lane & 7u)) << 4)), "r"(w & 0x11111111u),
+                             "r"(w & 0x22222222u), "r"(w & 0x44444444u), "r"((w >> 1) & 0x44444444u)
+                             : "memory");
+              }
             }
           }
-#if HB_GT_PROBE_STS < 8
-          if (cur[4 * sg] == 0x123456789ull) asm volatile("st.shared.b32 [%0], %1;" ::"r"(sB + stage * kStageBytes), "r"((uint32_t)cur[4 * sg + 1] + (uint32_t)cur[4 * sg + 2] + (uint32_t)cur[4 * sg + 3] + (uint32_t)cur[8 + 4 * sg] + (uint32_t)cur[9 + 4 * sg]+ (uint32_t)cur[10 + 4 * sg]+ (uint32_t)cur[11 + 4 * sg]) : "memory");
-#endif
 #ifdef HB_GT_DIAG
           dg_sts += clock64() - dg_s0;
 #endif
@@ -518,28 +516,10 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
           }
           if (lane == 0) mbar_arrive(bFull + 8 * stage);
           if (wi == 0) HB_TRACE(xt, 10 + kb);
-          if (++stage == kStages) {
-            stage = 0;
-            sphase ^= 1;
-          }
+          stage = (stage + 1) & (kStages - 1);
         }
-        stage += 2;  // the other group's pair
-        if (stage >= (uint32_t)kStages) {
-          stage -= kStages;
-          sphase ^= 1;
-        }
-        {
-          HB_DIAG_T0();
-#pragma unroll
-          for (int j = 0; j < 16; ++j) cur[j] = nxt[j];
-#ifdef HB_GT_DIAG
-          if (cur[0] == 0x1234567ull && cur[5] == 0x77ull && cur[10] == 1 && cur[15] == 3) ++xt;  // make the clock wait for the loads
-#endif
-          HB_DIAG_ADD(dg_mov);
-        }
-#ifdef HB_GT_DIAG
-        ++xt;
-#endif
+        stage = (stage + 2) & (kStages - 1);  // the other group's pair; four stages = one tile, so the phase flips per tile
+        sphase ^= 1;
       }
     }
 #ifdef HB_GT_DIAG
@@ -552,7 +532,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
       g_gt4_diag[blockIdx.x * 16 + 11] = dg_mov;
     }
 #endif
-  } else {
+  } else if (warp == kEpiWarps + kExpWarps) {
     // ===================== MMA issue: one elected thread =====================
     uint32_t stage = 0, sphase = 0, tcount = 0, it = 0;
     [[maybe_unused]] long long dg_tempty = 0, dg_full = 0;
@@ -607,6 +587,27 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
       g_gt4_diag[blockIdx.x * 16 + 2] = dg_full;
     }
 #endif
+  } else {
+    // ===================== loader: the tile's packed rows into the raw buffer, four bulk copies =====================
+    // (async proxy end to end: the copies complete on raw_full's transaction count, no thread waits on a load)
+    uint32_t xt = 0;
+    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+      const uint32_t chunk = item / p.n_qtiles;
+      const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
+      for (uint32_t t = t0; t < t1; ++t, ++xt) {
+        mbar_wait(bRawFree, (xt & 1) ^ 1);
+        const uint64_t row0 = (uint64_t)t * kTileN;
+        const uint32_t rows = (uint32_t)min((uint64_t)kTileN, p.n - row0);
+        if (lane == 0)
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bRawFull), "r"(rows * 128u) : "memory");
+        __syncwarp();
+        const uint32_t r = lane * kCopyRows;
+        if (r < rows)
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(sRaw + r * kRawPitch),
+                       "l"(p.data + (row0 + r) * 16), "r"(min(kCopyRows, rows - r) * 128u), "r"(bRawFull)
+                       : "memory");
+      }
+    }
   }
 
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
