@@ -201,8 +201,9 @@ GT_ALGOS = {"auto": 0, "scan": 1, "mma": 2, "mxf4": 3}  # hb_gt_algo
 
 def ground_truth(data, queries, k: int, device: int = 0, algo: str = "auto"):
     """CLI `ground-truth` (cli/src/main.rs:715-754): exact k smallest (distance, key) per query,
-    ascending; returns 0-based keys (nq,k) u64 and dists (nq,k) u64.  `algo`: "auto", "scan" (XOR+POPC) or
-    "mma" (tcgen05 int8 GEMM) -- identical results."""
+    ascending; returns 0-based keys (nq,k) u64 and dists (nq,k) u64.  `algo`: "auto", "scan" (XOR+POPC),
+    "mxf4" (tcgen05 GEMM on E2M1 operands, what "auto" picks for large batches) or "mma" (the same on int8) --
+    identical results."""
     d, q = _sketches(data) if len(data) else np.zeros((0, 16), dtype=np.uint64), _sketches(queries)
     keys = np.zeros((len(q), k), dtype=np.uint64)
     dists = np.zeros((len(q), k), dtype=np.uint64)

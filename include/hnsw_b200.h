@@ -160,9 +160,9 @@ int hb_ground_truth(const uint64_t* data, uint64_t n, const uint64_t* queries, u
 int hb_ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq,
                            uint32_t k, void* d_packed, void* stream);
 
-/* Kernel choice for the two calls above.  HB_GT_AUTO picks the tcgen05 int8 GEMM (gt_tcgen05.cu) for batches of
- * at least 32 queries over at least 4096 rows and the XOR+POPC scan (bruteforce.cu) otherwise; both are exact and
- * return identical lists.  The *_algo variants force one (HB_ERR_UNSUPPORTED if it cannot run the request). */
+/* Kernel choice for the two calls above.  HB_GT_AUTO picks the tcgen05 GEMM on E2M1 operands (gt_mxf4.cu) for batches
+ * of at least 32 queries over at least 4096 rows and the XOR+POPC scan (bruteforce.cu) otherwise; HB_GT_MMA is the
+ * same GEMM on int8 operands (gt_tcgen05.cu).  All three are exact and return identical lists.  The *_algo variants force one (HB_ERR_UNSUPPORTED if it cannot run the request). */
 typedef enum hb_gt_algo { HB_GT_AUTO = 0, HB_GT_SCAN = 1, HB_GT_MMA = 2, HB_GT_MXF4 = 3 } hb_gt_algo;
 int hb_ground_truth_algo(const uint64_t* data, uint64_t n, const uint64_t* queries, uint64_t nq, uint32_t k, int device,
                          int algo, uint64_t* keys, uint64_t* dists);
