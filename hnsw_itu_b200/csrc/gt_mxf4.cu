@@ -155,33 +155,62 @@ struct GtParams {
 };
 
 // k > 16: the row's candidates go to an UNORDERED append buffer of 2k slots in global memory (one store per accepted
-// row; the merge kernel needs no order).  When a buffer fills, the whole warp compacts it: the k-th smallest packed
-// value V is found by bisection on the 43 significant bits (every lane counts its share, REDUX adds), entries <= V
-// move to the front, the tail is cleared, and the row's threshold becomes V's distance.  Amortised over k appends,
-// against a dependent chain of loads per insert into a sorted list.  `buf` and the result are warp-uniform.
+// row; the merge kernel needs no order).  When a buffer is about to fill, the whole warp compacts it: entries up to the
+// k-th smallest move to the front, the tail is cleared, and the row's threshold becomes the k-th distance.  Amortised
+// over the appends in between, against a dependent chain of loads per insert into a sorted list.  `buf` and the result
+// are warp-uniform.
+// Returns (k-th smallest distance << 32) | entries kept.  The bisection runs on the distance alone, between the
+// smallest and largest distance in the buffer (7-10 passes instead of 43 over the packed value), and keeps every entry
+// up to and including the k-th distance -- a few more than k when that distance is tied, which is harmless: the row's
+// threshold is the distance, and rows arrive in increasing key order.  Only when the ties would leave less than
+// max(8, k/4) free slots does it bisect the keys of the tied entries as well and keep exactly k.
 __device__ __noinline__ uint64_t gt4_warp_compact(uint64_t* buf, uint32_t cap, uint32_t k) {
   const uint32_t lane = threadIdx.x & 31;
-  uint64_t lo = 0, hi = (1025ull << 32);  // smallest V with count(e <= V) >= k lies in [lo, hi]
-  while (lo < hi) {
-    const uint64_t mid = lo + ((hi - lo) >> 1);
+  uint32_t dmin = 0xFFFFFFFFu, dmax = 0;
+  for (uint32_t i = lane; i < cap; i += 32) {
+    const uint64_t e = buf[i];
+    if (e != kNone) {
+      dmin = min(dmin, (uint32_t)(e >> 32));
+      dmax = max(dmax, (uint32_t)(e >> 32));
+    }
+  }
+  uint32_t lo = __reduce_min_sync(0xFFFFFFFFu, dmin), hi = __reduce_max_sync(0xFFFFFFFFu, dmax);
+  while (lo < hi) {  // smallest distance d with count(dist <= d) >= k
+    const uint32_t mid = lo + ((hi - lo) >> 1);
     uint32_t c = 0;
-    for (uint32_t i = lane; i < cap; i += 32) c += (buf[i] <= mid) ? 1u : 0u;
+    for (uint32_t i = lane; i < cap; i += 32) c += ((uint32_t)(buf[i] >> 32) <= mid) ? 1u : 0u;
     c = __reduce_add_sync(0xFFFFFFFFu, c);
     if (c >= k) hi = mid;
     else lo = mid + 1;
+  }
+  uint32_t c_le = 0;
+  for (uint32_t i = lane; i < cap; i += 32) c_le += ((uint32_t)(buf[i] >> 32) <= lo) ? 1u : 0u;
+  c_le = __reduce_add_sync(0xFFFFFFFFu, c_le);
+  uint64_t V = ((uint64_t)lo << 32) | 0xFFFFFFFFull;
+  if (c_le + max(8u, k / 4) > cap) {  // heavy ties at the k-th distance: keep exactly k
+    uint64_t l64 = (uint64_t)lo << 32, h64 = V;
+    while (l64 < h64) {
+      const uint64_t mid = l64 + ((h64 - l64) >> 1);
+      uint32_t c = 0;
+      for (uint32_t i = lane; i < cap; i += 32) c += (buf[i] <= mid) ? 1u : 0u;
+      c = __reduce_add_sync(0xFFFFFFFFu, c);
+      if (c >= k) h64 = mid;
+      else l64 = mid + 1;
+    }
+    V = l64;
   }
   uint32_t woff = 0;
   for (uint32_t base = 0; base < cap; base += 32) {
     const uint32_t i = base + lane;
     const uint64_t e = (i < cap) ? buf[i] : kNone;
-    const uint32_t m = __ballot_sync(0xFFFFFFFFu, e <= lo);
-    if (e <= lo) buf[woff + __popc(m & ((1u << lane) - 1u))] = e;  // woff + rank <= i: never ahead of the reads
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, e <= V);
+    if (e <= V) buf[woff + __popc(m & ((1u << lane) - 1u))] = e;  // woff + rank <= i: never ahead of the reads
     woff += __popc(m);
     __syncwarp();
   }
   for (uint32_t i = woff + lane; i < cap; i += 32) buf[i] = kNone;
   __syncwarp();
-  return lo;
+  return ((uint64_t)lo << 32) | woff;
 }
 
 template <bool kRegList>
@@ -296,23 +325,75 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
         for (int g = 0; g < kTileN / kGroup; ++g) {
           uint32_t h0 = 0, h1 = 0;
           bool hit;
+          float m8[kGroup / 8];  // maxima of the group's six octets of columns
           {
             uint32_t v[kGroup];
             HB_TMEM_LD32(v, taddr + g * kGroup);
             HB_TMEM_LD16((v + 32), taddr + g * kGroup + 32);
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            float mx = __uint_as_float(v[0]);
 #pragma unroll
-            for (int c = 1; c < kGroup; c += 1) mx = fmaxf(mx, __uint_as_float(v[c]));
+            for (int j = 0; j < kGroup / 8; ++j) {
+              float a = __uint_as_float(v[8 * j]);
+#pragma unroll
+              for (int c = 1; c < 8; ++c) a = fmaxf(a, __uint_as_float(v[8 * j + c]));
+              m8[j] = a;
+            }
+            float mx = m8[0];
+#pragma unroll
+            for (int j = 1; j < kGroup / 8; ++j) mx = fmaxf(mx, m8[j]);
             hit = __any_sync(0xFFFFFFFFu, mx > Te);
-            if (hit) {  // warp-uniform: which columns pass for which lane
+            if (kRegList && hit) {  // warp-uniform: which columns pass for which lane
 #pragma unroll
               for (int c = 0; c < 32; ++c) h0 |= (uint32_t)(__uint_as_float(v[c]) > Te) << c;
 #pragma unroll
               for (int c = 0; c < kGroup - 32; ++c) h1 |= (uint32_t)(__uint_as_float(v[32 + c]) > Te) << c;
             }
           }
-          if (hit) {
+          if (!kRegList && hit) {
+            // k > 16: for every octet of columns some lane wants, all lanes re-read their eight values of it from TMEM
+            // (the accumulator is still ours) and append the ones that pass to their own buffers, in parallel and with
+            // static register indices.  A buffer that could overflow inside the octet is compacted first.
+            HB_DIAG_T0();
+            const uint64_t r0 = tile_row0 + (uint64_t)g * kGroup;
+            const uint32_t nvalid = (uint32_t)min((uint64_t)kGroup, row_end > r0 ? row_end - r0 : 0);
+            uint32_t fb = 0;
+#pragma unroll
+            for (int j = 0; j < kGroup / 8; ++j) fb |= (uint32_t)(m8[j] > Te) << j;
+            uint32_t um = __reduce_or_sync(0xFFFFFFFFu, fb);
+            while (um) {
+              const uint32_t c0 = 8u * ((uint32_t)__ffs((int)um) - 1u);
+              um &= um - 1;
+              if (c0 >= nvalid) break;
+              uint32_t fm = __ballot_sync(0xFFFFFFFFu, cnt + 8 > p.lcap);
+              while (fm) {
+                const int src = __ffs((int)fm) - 1;
+                fm &= fm - 1;
+                uint64_t* buf = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, reinterpret_cast<unsigned long long>(list), src));
+                __syncwarp();
+                const uint64_t kth = gt4_warp_compact(buf, p.lcap, p.k);
+                if ((int)lane == src) {
+                  cnt = (uint32_t)kth;
+                  atomicMin(gq, (uint32_t)(kth >> 32));
+                  T = (float)(popq - (int)(uint32_t)(kth >> 32));
+                  Te = fmaxf(T, Tg);
+                }
+              }
+              uint32_t w[8];
+              asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                           : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                           : "r"(taddr + g * kGroup + c0)
+                           : "memory");
+              asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float x = __uint_as_float(w[i]);
+                if (x > Te && c0 + i < nvalid)
+                  list[cnt++] = ((uint64_t)(uint32_t)(popq - (int)x) << 32) | (uint32_t)(p.key_offset + r0 + c0 + i);
+              }
+            }
+            HB_DIAG_ADD(dg_ins);
+          }
+          if (kRegList && hit) {
             // Rare path, kept warp-uniform: for every column some lane wants, each lane re-reads its own value of that
             // column from TMEM (the accumulator is still ours) and the lanes that pass run one copy of the insert.
             HB_DIAG_T0();
@@ -357,7 +438,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
                     uint64_t* buf = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, reinterpret_cast<unsigned long long>(list), src));
                     const uint64_t kth = gt4_warp_compact(buf, p.lcap, p.k);
                     if ((int)lane == src) {
-                      cnt = p.k;
+                      cnt = (uint32_t)kth;
                       atomicMin(gq, (uint32_t)(kth >> 32));
                       T = (float)(popq - (int)(uint32_t)(kth >> 32));
                       Te = fmaxf(T, Tg);
