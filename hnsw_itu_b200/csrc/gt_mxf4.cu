@@ -213,6 +213,60 @@ __device__ __noinline__ uint64_t gt4_warp_compact(uint64_t* buf, uint32_t cap, u
   return ((uint64_t)lo << 32) | woff;
 }
 
+// The same for buffers of at most 256 slots (k <= 128), held in registers: one read of the buffer instead of one per pass.
+__device__ __noinline__ uint64_t gt4_warp_compact_small(uint64_t* buf, uint32_t cap, uint32_t k) {
+  const uint32_t lane = threadIdx.x & 31;
+  uint64_t r[8];
+  uint32_t dmin = 0xFFFFFFFFu, dmax = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t i = lane + 32 * j;
+    r[j] = (i < cap) ? buf[i] : kNone;
+    if (r[j] != kNone) {
+      dmin = min(dmin, (uint32_t)(r[j] >> 32));
+      dmax = max(dmax, (uint32_t)(r[j] >> 32));
+    }
+  }
+  uint32_t lo = __reduce_min_sync(0xFFFFFFFFu, dmin), hi = __reduce_max_sync(0xFFFFFFFFu, dmax);
+  while (lo < hi) {
+    const uint32_t mid = lo + ((hi - lo) >> 1);
+    uint32_t c = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) c += ((uint32_t)(r[j] >> 32) <= mid) ? 1u : 0u;
+    c = __reduce_add_sync(0xFFFFFFFFu, c);
+    if (c >= k) hi = mid;
+    else lo = mid + 1;
+  }
+  uint32_t c_le = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) c_le += ((uint32_t)(r[j] >> 32) <= lo) ? 1u : 0u;
+  c_le = __reduce_add_sync(0xFFFFFFFFu, c_le);
+  uint64_t V = ((uint64_t)lo << 32) | 0xFFFFFFFFull;
+  if (c_le + max(8u, k / 4) > cap) {
+    uint64_t l64 = (uint64_t)lo << 32, h64 = V;
+    while (l64 < h64) {
+      const uint64_t mid = l64 + ((h64 - l64) >> 1);
+      uint32_t c = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) c += (r[j] <= mid) ? 1u : 0u;
+      c = __reduce_add_sync(0xFFFFFFFFu, c);
+      if (c >= k) h64 = mid;
+      else l64 = mid + 1;
+    }
+    V = l64;
+  }
+  uint32_t woff = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {  // every slot was read above, so the writes cannot overtake a read
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, r[j] <= V);
+    if (r[j] <= V) buf[woff + __popc(m & ((1u << lane) - 1u))] = r[j];
+    woff += __popc(m);
+  }
+  for (uint32_t i = woff + lane; i < cap; i += 32) buf[i] = kNone;
+  __syncwarp();
+  return ((uint64_t)lo << 32) | woff;
+}
+
 template <bool kRegList>
 __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) {
   extern __shared__ unsigned char smem_raw[];
@@ -370,7 +424,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
                 fm &= fm - 1;
                 uint64_t* buf = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, reinterpret_cast<unsigned long long>(list), src));
                 __syncwarp();
-                const uint64_t kth = gt4_warp_compact(buf, p.lcap, p.k);
+                const uint64_t kth = p.lcap <= 256 ? gt4_warp_compact_small(buf, p.lcap, p.k) : gt4_warp_compact(buf, p.lcap, p.k);
                 if ((int)lane == src) {
                   cnt = (uint32_t)kth;
                   atomicMin(gq, (uint32_t)(kth >> 32));
@@ -436,7 +490,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
                     const int src = __ffs((int)fm) - 1;
                     fm &= fm - 1;
                     uint64_t* buf = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, reinterpret_cast<unsigned long long>(list), src));
-                    const uint64_t kth = gt4_warp_compact(buf, p.lcap, p.k);
+                    const uint64_t kth = p.lcap <= 256 ? gt4_warp_compact_small(buf, p.lcap, p.k) : gt4_warp_compact(buf, p.lcap, p.k);
                     if ((int)lane == src) {
                       cnt = (uint32_t)kth;
                       atomicMin(gq, (uint32_t)(kth >> 32));
