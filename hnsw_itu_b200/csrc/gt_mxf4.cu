@@ -10,6 +10,8 @@
 // (E8M0, one per 32 elements) are all 0x7F = 2^0: sixteen TMEM columns are filled with that byte once, and since every
 // byte is equal the scale-factor layout does not matter.  Accumulator tiles are 128 x 240 (two of them + the scale
 // columns = 512 TMEM columns).  Everything else -- roles, barriers, lists, threshold sharing, merge -- is gt_tcgen05.cu's.
+#include <cuda.h>  // CUtensorMap and the encode entry point's signature (no libcuda link: resolved through the runtime)
+
 #include <algorithm>
 #include <climits>
 
@@ -34,13 +36,14 @@ constexpr int kThreads = (kEpiWarps + kExpWarps + 2) * 32;  // + the MMA warp + 
 constexpr uint32_t kABytes = kTileM * 512;            // 4 K-blocks x (128 rows x 128 B)
 constexpr uint32_t kAKBlockBytes = kTileM * 128;
 constexpr uint32_t kStageBytes = kTileN * 128;
-// the packed rows of one data tile as the bulk copies deliver them (a few large copies: one 128-byte copy per row
-// at a conflict-free pitch was tried and costs ~54 cycles per copy, 13 k cycles per tile)
+// the packed rows of one data tile as ONE tensor-map TMA copy delivers them: 128 B per row, 128-byte swizzle (the
+// 16-byte piece c of row r sits at piece c ^ (r & 7)), so the same piece of eight consecutive rows lies in eight
+// different bank groups.  (One 128-byte bulk copy per row at a padded pitch costs ~54 cycles per copy, 13 k cycles per
+// tile; four large unswizzled copies need lane-rotated reads and selects to dodge the conflicts: 34.4 ms.)
 constexpr uint32_t kRawPitch = 128, kRawBytes = kTileN * kRawPitch;
-constexpr uint32_t kCopyRows = 60;  // rows per bulk copy: four copies per tile
 constexpr uint32_t kRawOffset = kABytes + kStages * kStageBytes;
 constexpr uint32_t kBarOffset = kRawOffset + kRawBytes;
-static_assert(kStageBytes % 1024 == 0 && kRawOffset % 16 == 0 && kBarOffset % 8 == 0, "smem layout");
+static_assert(kStageBytes % 1024 == 0 && kRawOffset % 1024 == 0 && kBarOffset % 8 == 0, "smem layout");
 constexpr uint32_t kSmemBytes = kBarOffset + 192 + 1024;  // + barriers + alignment slack
 
 // instruction descriptor (cute::UMMA::InstrDescriptorBlockScaled layout): A = B = E2M1 (MXF4 format 1), both K-major,
@@ -268,7 +271,7 @@ __device__ __noinline__ uint64_t gt4_warp_compact_small(uint64_t* buf, uint32_t 
 }
 
 template <bool kRegList>
-__global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) {
+__global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, const __grid_constant__ CUtensorMap tmap) {
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;  // swizzle atoms need 1024-B alignment
@@ -584,33 +587,27 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
           mbar_wait(bRawFull, xt & 1);
           HB_DIAG_ADD(dg_top);
         }
-        // Rows are 128 B apart, so the same 16 bytes of eight consecutive rows share a bank group: lane l reads its
-        // four 16-byte pieces in the order (e + l) & 3 (two lanes per bank group, the floor for a 64-byte window) and
-        // two select stages put them back in order with static register indices.
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          const uint32_t lrow = 64 * wi + 32 * h + lane;
-          const bool valid = lrow < (uint32_t)kTileN && (uint64_t)t * kTileN + lrow < p.n;
-          const uint32_t ra = sRaw + (valid ? lrow : 0u) * kRawPitch + grp * 64;
-          uint32_t tmp[16];
+          const uint32_t lrow = 64 * wi + 32 * h + lane;  // lrow & 7 == lane & 7; rows past the data end arrive as zeros
+          const uint32_t ra = sRaw + (lrow < (uint32_t)kTileN ? lrow : 0u) * kRawPitch;
 #pragma unroll
           for (int e = 0; e < 4; ++e)
             asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(tmp[4 * e]), "=r"(tmp[4 * e + 1]), "=r"(tmp[4 * e + 2]), "=r"(tmp[4 * e + 3])
-                         : "r"(ra + 16 * (((uint32_t)e + lane) & 3u))
+                         : "=r"(cur[h][4 * e]), "=r"(cur[h][4 * e + 1]), "=r"(cur[h][4 * e + 2]), "=r"(cur[h][4 * e + 3])
+                         : "r"(ra + (((4u * grp + e) ^ (lane & 7u)) << 4))
                          : "memory");
-          const bool b0 = lane & 1u, b1 = lane & 2u;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {  // cur[4 j + i] = tmp[4 ((j - lane) & 3) + i]
-            const uint32_t a0 = tmp[i], a1 = tmp[4 + i], a2 = tmp[8 + i], a3 = tmp[12 + i];
-            const uint32_t c0 = b0 ? a3 : a0, c1 = b0 ? a0 : a1, c2 = b0 ? a1 : a2, c3 = b0 ? a2 : a3;
-            cur[h][i] = valid ? (b1 ? c2 : c0) : 0u;
-            cur[h][4 + i] = valid ? (b1 ? c3 : c1) : 0u;
-            cur[h][8 + i] = valid ? (b1 ? c0 : c2) : 0u;
-            cur[h][12 + i] = valid ? (b1 ? c1 : c3) : 0u;
-          }
         }
-        // the selects consumed every loaded word, so the reads have been performed: hand the buffer back right away
+        // hand the buffer back once the values have arrived (the XOR of all of them is a dependency on every load; it
+        // cannot be all ones for sixteen words of real data and the store below never happens)
+        {
+          uint32_t dep = 0;
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int e = 0; e < 16; ++e) dep |= cur[h][e];
+          if (dep == 0xFFFFFFFFu && t == 0xFFFFFFFFu) asm volatile("st.shared.b32 [%0], %1;" ::"r"(sRaw), "r"(dep) : "memory");
+        }
         // (the copy for the next tile then has this whole tile's expansion time to land)
         __syncwarp();
         if (lane == 0) mbar_arrive(bRawFree);
@@ -723,7 +720,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
     }
 #endif
   } else {
-    // ===================== loader: the tile's packed rows into the raw buffer, four bulk copies =====================
+    // ===================== loader: the tile's packed rows into the raw buffer, one TMA copy =====================
     // (async proxy end to end: the copies complete on raw_full's transaction count, no thread waits on a load)
     uint32_t xt = 0;
     for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
@@ -731,16 +728,13 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p) 
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
       for (uint32_t t = t0; t < t1; ++t, ++xt) {
         mbar_wait(bRawFree, (xt & 1) ^ 1);
-        const uint64_t row0 = (uint64_t)t * kTileN;
-        const uint32_t rows = (uint32_t)min((uint64_t)kTileN, p.n - row0);
-        if (lane == 0)
-          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bRawFull), "r"(rows * 128u) : "memory");
-        __syncwarp();
-        const uint32_t r = lane * kCopyRows;
-        if (r < rows)
-          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(sRaw + r * kRawPitch),
-                       "l"(p.data + (row0 + r) * 16), "r"(min(kCopyRows, rows - r) * 128u), "r"(bRawFull)
+        if (lane == 0) {
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bRawFull), "r"(kRawBytes) : "memory");
+          asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(sRaw),
+                       "l"(&tmap), "r"(0), "r"((int)(t * (uint32_t)kTileN)), "r"(bRawFull)
                        : "memory");
+        }
+        __syncwarp();
       }
     }
   }
@@ -760,6 +754,23 @@ extern "C" int hb_debug_gt4_diag(long long* out) {
   return (int)cudaMemcpyFromSymbol(out, g_gt4_diag, sizeof(long long) * 256 * 16);
 }
 #endif
+
+namespace {
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (the library does not link libcuda)
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult st = cudaDriverEntryPointSymbolNotFound;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &st) != cudaSuccess || st != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(f);
+  }();
+  return fn;
+}
+}  // namespace
 
 bool ground_truth_mxf4_supported(const void* d_data, const void* d_queries, uint64_t n, uint64_t nq, uint32_t k) {
   return n >= 1 && nq >= 1 && k >= 1 && k <= 1024 && (reinterpret_cast<uintptr_t>(d_data) & 31) == 0 &&
@@ -814,14 +825,33 @@ void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offse
   p.partial = partial;
   p.gthr = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(partial) + list_bytes);
   HB_CUDA(cudaMemsetAsync(p.gthr, 0xFF, nq * 4, stream));
+  // the packed rows as a 2-D tensor of 32-bit words, n rows x 32; one box = one data tile, 128-byte swizzled, rows past
+  // the end filled with zeros
+  CUtensorMap tmap;
+  {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) {
+      cudaFreeAsync(partial, stream);
+      HB_REQUIRE(false, HB_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled is not available from this driver");
+    }
+    const cuuint64_t gdim[2] = {32, n}, gstride[1] = {128};
+    const cuuint32_t box[2] = {32, (cuuint32_t)kTileN}, estride[2] = {1, 1};
+    const CUresult r = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(d_data), gdim, gstride, box, estride,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+      cudaFreeAsync(partial, stream);
+      HB_REQUIRE(false, HB_ERR_CUDA, "cuTensorMapEncodeTiled failed");
+    }
+  }
   const uint32_t n_items = p.n_qtiles * p.n_chunks;
   const uint32_t grid = std::min<uint32_t>(n_items, (uint32_t)sms);
   if (k <= 16) {
     HB_CUDA(cudaFuncSetAttribute(gt_mxf4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    gt_mxf4_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(p);
+    gt_mxf4_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(p, tmap);
   } else {
     HB_CUDA(cudaFuncSetAttribute(gt_mxf4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    gt_mxf4_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(p);
+    gt_mxf4_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(p, tmap);
   }
   count_launches();
   cudaError_t e = cudaGetLastError();
