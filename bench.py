@@ -197,14 +197,17 @@ def main():
             del data
         gt = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
         # exact ground truth for the recall figure = BASELINE.json configs[3] on one GPU (the `ground-truth` path as a
-        # tcgen05 int8 GEMM with fused top-k); timed here with CUDA events, second of two calls, reported beside the headline
+        # tcgen05 GEMM on E2M1 operands with fused top-k); timed here with CUDA events, best of the three calls after one
+        # warm-up call, reported beside the headline
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        for _ in range(2):
+        gt_ms = None
+        for i in range(4):
             g0.record()
             _lib.check(lib.hb_ground_truth_device(d_data.data_ptr(), a.n, 0, dq.data_ptr(), a.nq, a.k, gt.data_ptr(), None))
             g1.record()
             torch.cuda.synchronize()
-        gt_ms = g0.elapsed_time(g1)
+            if i:
+                gt_ms = g0.elapsed_time(g1) if gt_ms is None else min(gt_ms, g0.elapsed_time(g1))
         gt_keys = gt.cpu().numpy().view(np.uint64) & np.uint64(0xFFFFFFFF)
         del d_data, gt
         torch.cuda.empty_cache()
