@@ -192,12 +192,12 @@ void unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists
 }
 
 void ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
-                         void* d_packed, cudaStream_t stream, int algo) {
+                         void* d_packed, cudaStream_t stream, int algo, uint32_t* d_bound) {
   HB_REQUIRE(algo == HB_GT_AUTO || algo == HB_GT_SCAN || algo == HB_GT_MMA || algo == HB_GT_MXF4, HB_ERR_INVALID, "unknown ground-truth algorithm");
   if (algo == HB_GT_AUTO)
     algo = (nq >= 32 && n >= 4096 && ground_truth_mxf4_supported(d_data, d_queries, n, nq, k)) ? HB_GT_MXF4 : HB_GT_SCAN;
   if (algo == HB_GT_MXF4)
-    ground_truth_mxf4_device(d_data, n, key_offset, d_queries, nq, k, d_packed, stream);
+    ground_truth_mxf4_device(d_data, n, key_offset, d_queries, nq, k, d_packed, stream, d_bound);
   else if (algo == HB_GT_MMA)
     ground_truth_mma_device(d_data, n, key_offset, d_queries, nq, k, d_packed, stream);
   else

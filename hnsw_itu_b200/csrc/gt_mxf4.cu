@@ -778,7 +778,7 @@ bool ground_truth_mxf4_supported(const void* d_data, const void* d_queries, uint
 }
 
 void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
-                             void* d_packed, cudaStream_t stream) {
+                             void* d_packed, cudaStream_t stream, uint32_t* d_bound) {
   HB_REQUIRE(ground_truth_mxf4_supported(d_data, d_queries, n, nq, k), HB_ERR_UNSUPPORTED,
              "tcgen05 ground truth: needs 32-byte aligned data, 1 <= k <= 1024");
   HB_REQUIRE(key_offset + n <= 0xFFFFFFFFull, HB_ERR_UNSUPPORTED, "keys must stay below 2^32");
@@ -823,8 +823,12 @@ void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offse
   const size_t list_bytes = (size_t)p.n_chunks * nq * p.lcap * 8;
   HB_CUDA(cudaMallocAsync(&partial, list_bytes + nq * 4, stream));
   p.partial = partial;
-  p.gthr = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(partial) + list_bytes);
-  HB_CUDA(cudaMemsetAsync(p.gthr, 0xFF, nq * 4, stream));
+  if (d_bound) {
+    p.gthr = d_bound;  // carried over from the caller's earlier slices
+  } else {
+    p.gthr = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(partial) + list_bytes);
+    HB_CUDA(cudaMemsetAsync(p.gthr, 0xFF, nq * 4, stream));
+  }
   // the packed rows as a 2-D tensor of 32-bit words, n rows x 32; one box = one data tile, 128-byte swizzled, rows past
   // the end filled with zeros
   CUtensorMap tmap;

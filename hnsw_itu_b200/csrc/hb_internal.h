@@ -120,8 +120,12 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
                  void* d_dists, void* d_found, void* d_counters, cudaStream_t stream);
 
 // bruteforce.cu
+// d_bound (optional, nq u32, 0xFFFFFFFF = none yet): per-query upper bound on the global k-th distance, read and
+// tightened by the E2M1 kernel.  A caller that searches one data set slice by slice passes the same array to every
+// call so that later slices start with the earlier slices' bound; the per-slice lists may then hold fewer than k rows
+// (the rest cannot be in the global top-k) and the exact merge of the slices is unchanged.
 void ground_truth_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
-                         void* d_packed, cudaStream_t stream, int algo = HB_GT_AUTO);
+                         void* d_packed, cudaStream_t stream, int algo = HB_GT_AUTO, uint32_t* d_bound = nullptr);
 void ground_truth_scan_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
                               void* d_packed, cudaStream_t stream);
 // gt_tcgen05.cu
@@ -131,7 +135,7 @@ void ground_truth_mma_device(const void* d_data, uint64_t n, uint64_t key_offset
 // the same GEMM with E2M1 operands (tcgen05.mma kind::mxf4.block_scale, unit scales); gt_mxf4.cu
 bool ground_truth_mxf4_supported(const void* d_data, const void* d_queries, uint64_t n, uint64_t nq, uint32_t k);
 void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
-                             void* d_packed, cudaStream_t stream);
+                             void* d_packed, cudaStream_t stream, uint32_t* d_bound = nullptr);
 void topk_merge_device(const void* d_lists, uint32_t n_lists, uint64_t nq, uint32_t k, void* d_out, cudaStream_t stream,
                        bool sorted = true, uint32_t width = 0);  // !sorted: lists of `width` (default k) slots in any order, kNone = none
 void unpack_device(const void* d_packed, uint64_t n, void* d_keys, void* d_dists, cudaStream_t stream);

@@ -24,6 +24,8 @@
 
 #include "hb_internal.h"
 
+#include <atomic>
+
 namespace hb {
 
 namespace {
@@ -66,6 +68,19 @@ void ensure_device(int device) {
   }
   HB_REQUIRE(device >= 0 && device < count, HB_ERR_INVALID, "device ordinal out of range");
   HB_CUDA(cudaSetDevice(device));
+  // The stream-ordered allocations of the kernels' scratch (cudaMallocAsync) come from the device's default pool,
+  // which by default returns its memory to the driver at every synchronisation: keep up to 4 GB cached so that
+  // repeated calls do not pay for the allocation again.
+  static std::atomic<uint64_t> configured{0};
+  if (device < 64 && !(configured.load() >> device & 1)) {
+    cudaMemPool_t pool = nullptr;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      uint64_t keep = 4ull << 30;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    cudaGetLastError();
+    configured.fetch_or(1ull << device);
+  }
 }
 
 Index::~Index() {

@@ -319,7 +319,7 @@ def test_sharded_hnsw_pack_and_merge(hb, oracle):
 @pytest.mark.parametrize("k", [10, 100])
 def test_ground_truth_large_properties(hb, k):
     """Size-independent checks at a size the oracle would not finish in seconds (2 M x 1 k, generated on the device):
-    tcgen05 kernel == scan kernel bit for bit; rows ascend in (distance, key) with unique keys; every returned distance
+    both tcgen05 kernels == scan kernel bit for bit; rows ascend in (distance, key) with unique keys; every returned distance
     is recomputed from the sketches; queries that are data rows find themselves at distance 0."""
     import torch
     from hnsw_itu_b200 import _lib
@@ -331,13 +331,13 @@ def test_ground_truth_large_properties(hb, k):
     members = torch.arange(0, 64, device="cuda") * 31_013 + 7          # 64 queries are copies of data rows
     q[:64] = d[members]
     out = {}
-    for algo in (2, 1):
+    for algo in (3, 2, 1):                                              # E2M1 GEMM, int8 GEMM, XOR+POPC scan
         p = torch.empty((nq, k), dtype=torch.int64, device="cuda")
         _lib.check(_lib.lib().hb_ground_truth_device_algo(d.data_ptr(), n, 0, q.data_ptr(), nq, k, algo, p.data_ptr(), None))
         torch.cuda.synchronize()
         out[algo] = p.cpu().numpy().view(np.uint64)
-    assert np.array_equal(out[1], out[2])
-    packed = out[2]
+    assert np.array_equal(out[1], out[2]) and np.array_equal(out[1], out[3])
+    packed = out[3]
     assert (packed[:, 1:] > packed[:, :-1]).all()                       # strictly ascending (distance << 32 | key): unique keys
     keys, dists = (packed & np.uint64(0xFFFFFFFF)).astype(np.int64), (packed >> np.uint64(32)).astype(np.int64)
     assert keys.max() < n
@@ -347,6 +347,28 @@ def test_ground_truth_large_properties(hb, k):
     ref = np.unpackbits(x.view(np.uint8), axis=-1).sum(-1)
     assert np.array_equal(ref, dists[rows])
     assert (dists[:64, 0] == 0).all() and (keys[:64, 0] <= members.cpu().numpy()).all()
+
+
+def test_ground_truth_host_buffers_sliced_upload(hb):
+    """hb_ground_truth on host buffers above the slice size (2^21 rows): the rows are uploaded in slices while the
+    previous slice is searched, per-slice lists are merged exactly -- same lists as one search over the resident rows."""
+    import torch
+    from hnsw_itu_b200 import _lib
+    n, nq, k = 4_500_000, 256, 10                                       # three slices, the last one ragged
+    d = torch.empty((n, 16), dtype=torch.int64, device="cuda")
+    q = torch.empty((nq, 16), dtype=torch.int64, device="cuda")
+    hb.synth_sketches(d.data_ptr(), n, 2003)
+    hb.synth_sketches(q.data_ptr(), nq, 2004)
+    q[:8] = d[torch.tensor([0, 2_097_151, 2_097_152, 4_194_303, 4_194_304, 4_499_999, 17, 3_000_000], device="cuda")]  # slice borders
+    p = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    _lib.check(_lib.lib().hb_ground_truth_device(d.data_ptr(), n, 0, q.data_ptr(), nq, k, p.data_ptr(), None))
+    torch.cuda.synchronize()
+    ref = p.cpu().numpy().view(np.uint64)
+    hd, hq = d.cpu().numpy().view(np.uint64), q.cpu().numpy().view(np.uint64)
+    del d, p
+    keys, dists = hb.ground_truth(hd, hq, k)
+    assert np.array_equal((dists << np.uint64(32)) | keys, ref)
+    assert (dists[:8, 0] == 0).all()
 
 
 def test_knns_pinned_buffers_used_in_place(hb, oracle):
