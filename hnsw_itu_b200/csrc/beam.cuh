@@ -495,6 +495,27 @@ __device__ __forceinline__ void prefetch_row_sketches(const uint4* __restrict__ 
 // into L2, and once c_{t+1}'s row words have arrived the sketches of its neighbours are prefetched into L2.  A wrong
 // prediction (a neighbour accepted in this expansion overtakes them) falls back to plain loads; results never
 // depend on the prediction.
+// The recently-seen cache: "was this id evaluated lately?"  Lossy on purpose (a forgotten id is evaluated again and
+// rejected by the beam's own membership test); never claims an id it has not stored.  HB_CACHE_WAYS = 2: sets of two
+// entries, most recent first (one 64-bit read, one 64-bit write), same number of entries as the direct-mapped table.
+#ifndef HB_CACHE_WAYS
+#define HB_CACHE_WAYS 2
+#endif
+__device__ __forceinline__ bool cache_test_and_set(const WarpScratch& ws, uint32_t id) {
+#if HB_CACHE_WAYS == 2
+  uint2* set = reinterpret_cast<uint2*>(ws.cache) + ((id * 0x9E3779B1u) >> (ws.cache_shift + 1));
+  const uint2 e = *set;
+  if (e.x == id || e.y == id) return false;
+  *set = make_uint2(id, e.x);
+  return true;
+#else
+  const uint32_t h = (id * 0x9E3779B1u) >> ws.cache_shift;
+  const bool isnew = ws.cache[h] != id;
+  if (isnew) ws.cache[h] = id;
+  return isnew;
+#endif
+}
+
 template <class Beam>
 __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint32_t ef, uint32_t ep, const WarpScratch& ws,
                                             uint32_t* spill, uint32_t spill_cap, Beam& b, SearchCounters& c,
@@ -503,7 +524,7 @@ __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint3
   const uint32_t lt_mask = (1u << lane) - 1u;
   {
     const uint32_t d0 = hamming1(gv.sk, ep, qv);  // nsw.rs:140-141
-    if (lane == 0) ws.cache[(ep * 0x9E3779B1u) >> ws.cache_shift] = ep;  // nsw.rs:143-144
+    if (lane == 0) cache_test_and_set(ws, ep);  // nsw.rs:143-144
     b.reset(bm_pack(d0, ep));                                           // nsw.rs:145-146
     ++c.V;
     __syncwarp();
@@ -576,9 +597,7 @@ __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint3
         const bool valid = (wi >= 1u) && (wi <= deg) && w0 != kNoKey;  // 0xFFFFFFFF: builder tombstone
         bool isnew = false;
         if (valid) {
-          const uint32_t h = (w0 * 0x9E3779B1u) >> ws.cache_shift;
-          isnew = ws.cache[h] != w0;
-          if (isnew) ws.cache[h] = w0;
+          isnew = cache_test_and_set(ws, w0);
         }
         const uint32_t nm = __ballot_sync(kFullMask, isnew);
         if (isnew) ws.ids[__popc(nm & lt_mask)] = w0;
@@ -589,9 +608,7 @@ __device__ __forceinline__ void beam_search(const GraphView& gv, uint4 qv, uint3
         const bool valid = (wi <= deg) && w1 != kNoKey;
         bool isnew = false;
         if (valid) {
-          const uint32_t h = (w1 * 0x9E3779B1u) >> ws.cache_shift;
-          isnew = ws.cache[h] != w1;
-          if (isnew) ws.cache[h] = w1;
+          isnew = cache_test_and_set(ws, w1);
         }
         const uint32_t nm = __ballot_sync(kFullMask, isnew);
         if (isnew) ws.ids[n_new + __popc(nm & lt_mask)] = w1;
