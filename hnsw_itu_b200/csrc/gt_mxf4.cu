@@ -1,15 +1,20 @@
-// gt_mxf4.cu -- the `ground-truth` GEMM of gt_tcgen05.cu with 4-bit operands: tcgen05.mma kind::mxf4 (block-scaled
-// E2M1, all scale factors 1.0).  Same identity, Hamming(q, d) = pop(q) - sum_i (2 q_i - 1) d_i, same pipeline, same
-// fused top-k; what changes is the operand encoding and therefore the three resources that paced the int8 kernel:
-//   * the tensor pipe runs K = 64 per instruction instead of 32 (half the MMA time per tile),
-//   * a data row expands to 512 bytes instead of 1024 (half the shared-memory stores, 5 logic ops per 32 elements),
-//   * the query tile takes 64 KB instead of 128 KB, which buys five pipeline stages instead of three.
-// E2M1 holds +-{0.5, 1, 2} exactly: data bit at nibble position u -> {0.5, 1, 2, 2}, query bit -> +-{2, 1, 0.5, 0.5}, so every
-// product is +-1 or 0 and the fp32 accumulator holds the integer pop(q) - Hamming exactly (|acc| <= 1024).  Both
-// operands use the same physical nibble layout, so the K permutation this implies cancels.  The block scale factors
-// (E8M0, one per 32 elements) are all 0x7F = 2^0: sixteen TMEM columns are filled with that byte once, and since every
-// byte is equal the scale-factor layout does not matter.  Accumulator tiles are 128 x 240 (two of them + the scale
-// columns = 512 TMEM columns).  Everything else -- roles, barriers, lists, threshold sharing, merge -- is gt_tcgen05.cu's.
+// gt_mxf4.cu -- the `ground-truth` GEMM with 4-bit operands: tcgen05.mma kind::mxf4 (block-scaled E2M1, all scale
+// factors 1.0).  Identity: Hamming(q, d) = pop(q) - sum_i (2 q_i - 1) d_i.
+//
+// Encoding.  E2M1 holds +-{0.5, 1, 2} exactly: the data bit at nibble position u becomes {0.5, 1, 2, 2}, the query bit
+// +-{2, 1, 0.5, 0.5}, so every product is +-1 or 0 and the fp32 accumulator holds the integer pop(q) - Hamming exactly
+// (|acc| <= 1024).  Both operands use the same physical nibble layout, so the K permutation this implies cancels.  The
+// block scale factors (E8M0, one per 32 elements) are all 0x7F = 2^0: sixteen TMEM columns are filled with that byte
+// once, and since every byte is equal the scale-factor layout does not matter.  Against the int8 formulation
+// (gt_tcgen05.cu): K = 64 per instruction instead of 32, a data row expands to 512 bytes instead of 1024 (five logic
+// ops per 32 elements), the query tile takes 64 KB instead of 128 KB.
+//
+// Structure.  One persistent CTA per SM, 14 warps: 0-3 epilogue (thread = query row; fused top-k, threshold shared
+// across work items), 4-11 expansion in two groups (group g writes K-blocks 2g, 2g+1 of every tile, so one group
+// stores while the other sits in its proxy fence), 12 MMA issue, 13 loader (one swizzling tensor-map TMA copy per
+// data tile into a raw buffer: no thread waits on a global load).  Shared memory: query tile 64 KB + 4 stages x 30 KB
+// + raw tile 30 KB.  TMEM: two 128 x 240 fp32 accumulators + the scale columns = 512 columns.  Lists, compaction and
+// the exact merge follow gt_tcgen05.cu; DESIGN.md 4.3 has the measurements behind each of these choices.
 #include <cuda.h>  // CUtensorMap and the encode entry point's signature (no libcuda link: resolved through the runtime)
 
 #include <algorithm>
@@ -530,7 +535,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
     const uint32_t et = ew * 32 + lane;  // 0..255: thread of the expansion role (the query-tile fill is indexed by it)
     const uint32_t grp = ew & 1u, wi = ew >> 1;
     uint32_t stage = 2 * grp, sphase = 0, it = 0;
-    [[maybe_unused]] long long dg_empty = 0, dg_fence = 0, dg_afree = 0, dg_top = 0, dg_sts = 0, dg_mov = 0;
+    [[maybe_unused]] long long dg_empty = 0, dg_fence = 0, dg_afree = 0, dg_top = 0, dg_sts = 0;
     uint32_t xt = 0;  // tiles so far: parity of the raw buffer
     for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
@@ -661,7 +666,6 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
       g_gt4_diag[blockIdx.x * 16 + 8] = dg_afree;
       g_gt4_diag[blockIdx.x * 16 + 9] = dg_top;
       g_gt4_diag[blockIdx.x * 16 + 10] = dg_sts;
-      g_gt4_diag[blockIdx.x * 16 + 11] = dg_mov;
     }
 #endif
   } else if (warp == kEpiWarps + kExpWarps) {

@@ -23,7 +23,7 @@ print("ms", e0.elapsed_time(e1))
 buf = np.zeros(256 * 16, dtype=np.int64)
 assert getattr(L, "hb_debug_gt_diag" if ALGO == "mma" else "hb_debug_gt4_diag")(buf.ctypes.data_as(C.c_void_p)) == 0
 g = buf.reshape(256, 16)[:148]
-names = ["kernel", "mma:wait_acc_free", "mma:wait_stage_full", "exp:wait_stage_empty", "exp:fence", "epi:wait_acc_full", "epi:insert", "tiles", "exp:wait_A_free", "exp:wait_raw_full", "exp:stores", "-"]
+names = ["kernel", "mma:wait_acc_free", "mma:wait_stage_full", "exp:wait_stage_empty", "exp:fence", "epi:wait_acc_full", "epi:insert", "tiles", "exp:wait_A_free", "exp:wait_raw_full", "exp:stores"]
 tiles = g[:, 7].astype(float)
 print("tiles/CTA min/mean/max", tiles.min(), tiles.mean(), tiles.max())
 for i, n in enumerate(names):
