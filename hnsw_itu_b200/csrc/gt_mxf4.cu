@@ -533,7 +533,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
     // ===================== expansion: packed bits -> E2M1 operands in shared memory =====================
     const uint32_t ew = warp - kEpiWarps;
     const uint32_t et = ew * 32 + lane;  // 0..255: thread of the expansion role (the query-tile fill is indexed by it)
-    const uint32_t grp = ew & 1u, wi = ew >> 1;
+    const uint32_t grp = ew >> 2, wi = ew & 3u;  // a group = one warp on each SM sub-partition (warp id % 4)
     uint32_t stage = 2 * grp, sphase = 0, it = 0;
     [[maybe_unused]] long long dg_empty = 0, dg_fence = 0, dg_afree = 0, dg_top = 0, dg_sts = 0;
     uint32_t xt = 0;  // tiles so far: parity of the raw buffer
