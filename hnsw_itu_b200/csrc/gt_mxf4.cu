@@ -25,6 +25,9 @@
 #ifndef HB_GT_PROBE_MMAS
 #define HB_GT_PROBE_MMAS 4
 #endif
+#ifndef HB_GT_SUSPEND_NS
+#define HB_GT_SUSPEND_NS 20000u  // upper bound of one mbarrier.try_wait suspension
+#endif
 
 namespace hb {
 namespace {
@@ -70,12 +73,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   for (uint32_t spins = 0; !done; ++spins) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(done)
-        : "r"(bar), "r"(parity)
+        : "r"(bar), "r"(parity), "r"(HB_GT_SUSPEND_NS)  // suspend-time hint: the warp sleeps in the barrier unit instead of spinning
         : "memory");
-    if (!done && (spins & 1023u) == 1023u) {
+    if (!done && (spins & 15u) == 15u) {
       const long long now = clock64();
       if (t0 == 0) t0 = now;
       else if (now - t0 > 6000000000ll) __trap();  // ~3 s: no wait in this kernel is longer than a few ms
