@@ -385,7 +385,7 @@ def main():
                          "peak": 4.0 * bf16, "frac": tops / (4.0 * bf16),
                          "peak_source": "4 x MEASURED_PEAKS.json bf16_tflops (no fp4 figure is measured; nominal dense fp4 is 9000, int8 4500)",
                          "frac_of_nominal_9000": tops / 9000.0,
-                         "note": "tensor pipe 79 % active in the ncu capture (profiles/r01i_gt_mxf4_kernel_ncu_summary.json); the rest is the "
+                         "note": "tensor pipe 80 % active in the ncu capture (profiles/r01k_gt_mxf4_kernel_ncu_summary.json); the rest is the "
                                  "epilogue at the TMEM read rate and the operand expansion sharing issue slots (DESIGN.md 4.3)"}}
     print(json.dumps(line), flush=True)
     if world > 1:
