@@ -826,7 +826,10 @@ void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offse
   p.n_chunks = (p.n_tiles + p.tiles_per_chunk - 1) / p.tiles_per_chunk;
 
   uint64_t* partial = nullptr;
-  p.lcap = k <= 16 ? k : 2 * k;
+#ifndef HB_GT_LCAP_MULT
+#define HB_GT_LCAP_MULT 2  // append-buffer slots per row = this x k (measured: 3 and 4 are not faster, profiles/r01k_*)
+#endif
+  p.lcap = k <= 16 ? k : HB_GT_LCAP_MULT * k;
   const size_t list_bytes = (size_t)p.n_chunks * nq * p.lcap * 8;
   HB_CUDA(cudaMallocAsync(&partial, list_bytes + nq * 4, stream));
   p.partial = partial;
