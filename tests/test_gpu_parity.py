@@ -349,6 +349,27 @@ def test_ground_truth_large_properties(hb, k):
     assert (dists[:64, 0] == 0).all() and (keys[:64, 0] <= members.cpu().numpy()).all()
 
 
+@pytest.mark.parametrize("k", [10, 100, 1000])
+def test_ground_truth_all_rows_tied(hb, k):
+    """Every row at the same distance from every query (identical rows, plus a block of rows one bit closer in the
+    middle): the top-k is decided by the keys alone, the per-row thresholds never separate anything, and the append
+    buffers fill with ties (the compaction's key-bisection fallback).  Expected lists are known in closed form."""
+    n, nq = 6000, 40
+    base = np.full(16, 0x5555555555555555, dtype=np.uint64)
+    data = np.tile(base, (n, 1))
+    closer = np.arange(3000, 3000 + 7)                      # seven rows that differ from the rest in bit 0 of word 0
+    data[closer, 0] ^= np.uint64(1)
+    q = np.tile(base, (nq, 1))
+    q[:, 0] ^= np.uint64(1)                                 # queries equal the `closer` rows: distance 0 to them, 1 to the rest
+    q[1::2, 15] ^= np.uint64(0xFF00)                        # odd queries 8 bits further from everything
+    exp_keys = np.concatenate([closer, np.setdiff1d(np.arange(n), closer)])[:k].astype(np.uint64)
+    for algo in ("mxf4", "mma", "scan"):
+        gk, gd = hb.ground_truth(data, q, k, algo=algo)
+        assert np.array_equal(gk, np.tile(exp_keys, (nq, 1))), algo
+        d0 = np.where(np.arange(k) < 7, 0, 1).astype(np.uint64)
+        assert np.array_equal(gd[0::2], np.tile(d0, (nq // 2, 1))) and np.array_equal(gd[1::2], np.tile(d0 + np.uint64(8), (nq // 2, 1))), algo
+
+
 def test_ground_truth_host_buffers_sliced_upload(hb):
     """hb_ground_truth on host buffers above the slice size (2^21 rows): the rows are uploaded in slices while the
     previous slice is searched, per-slice lists are merged exactly -- same lists as one search over the resident rows."""
