@@ -485,6 +485,7 @@ int hb_ground_truth_algo(const uint64_t* data, uint64_t n, const uint64_t* queri
     if (nq == 0) return;
     DevMem<uint64_t> dd(n * 16), dq(nq * 16), dp(nq * k), dk(nq * k), ds(nq * k);
     HB_CUDA(cudaMemcpy(dq.p, queries, nq * 128, cudaMemcpyHostToDevice));
+    HB_CUDA(cudaDeviceSynchronize());  // the kernels below run on non-blocking streams, which the NULL stream does not order
     // Large inputs: the rows go up in slices (host threads staging through page-locked slots, StagedUploader) while the
     // previous slice is searched (the upload of 10 M rows takes longer than searching them); every slice yields an ascending list per query with global
     // keys, and the exact merge kernel combines them.  Small inputs: one copy, one search.

@@ -419,7 +419,7 @@ uint32_t ceil_log2(uint64_t x) {
 
 void ensure_common(const Index& idx, uint64_t nq);
 
-void ensure_workspace(const Index& idx, uint32_t vcap_log2, uint32_t slots, uint64_t nq) {
+void ensure_workspace(const Index& idx, uint32_t vcap_log2, uint32_t slots, uint64_t nq, cudaStream_t stream) {
   SearchWorkspace& ws = idx.ws;
   if (ws.vcap_log2 != vcap_log2 || ws.slots < slots) {
     cudaFree(ws.vis);
@@ -429,7 +429,8 @@ void ensure_workspace(const Index& idx, uint32_t vcap_log2, uint32_t slots, uint
     ws.slots = 0;
     const size_t words = (size_t)slots << vcap_log2;
     HB_CUDA(cudaMalloc(&ws.vis, words * 4));
-    HB_CUDA(cudaMemset(ws.vis, 0xFF, words * 4));
+    // on the LAUNCH stream: the caller's stream may be non-blocking, i.e. not ordered after the NULL stream
+    HB_CUDA(cudaMemsetAsync(ws.vis, 0xFF, words * 4, stream));
     ws.spill_cap = 1u << (vcap_log2 > 2 ? vcap_log2 - 2 : 0);
     HB_CUDA(cudaMalloc(&ws.spill, (size_t)slots * ws.spill_cap * 4));
     ws.vcap_log2 = vcap_log2;
@@ -559,7 +560,7 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     uint32_t blocks = (uint32_t)std::min<uint64_t>(max_blocks, (todo + kWarpsPerBlock - 1) / kWarpsPerBlock);
     // bound scratch memory for the (rare) big-table retries
     while (blocks > 1 && ((size_t)blocks * kWarpsPerBlock << vcap_log2) * 4 > (size_t)2 << 30) blocks = (blocks + 1) / 2;
-    ensure_workspace(idx, vcap_log2, blocks * kWarpsPerBlock, nq);
+    ensure_workspace(idx, vcap_log2, blocks * kWarpsPerBlock, nq, stream);
     const SearchWorkspace& ws = idx.ws;
     p.vis = ws.vis;
     p.spill = ws.spill;

@@ -178,16 +178,15 @@ def index_from_parts(algo: str, graphs: list[dict], ep: int | None, device: int 
     dn = (_u64p * ng)()
     of = (_u64p * ng)()
     ids = (C.c_void_p * ng)()
-    id_bytes = 8
+    # one id width for every graph (the C ABI takes a single id_bytes): u32 only when every graph passes u32
+    all_ids = [np.asarray(g.get("ids", np.zeros(0, dtype=np.uint64))) for g in graphs]
+    id_bytes = 4 if all_ids and all(x.dtype == np.uint32 for x in all_ids) else 8
+    id_dtype = np.uint32 if id_bytes == 4 else np.uint64
     for i, g in enumerate(graphs):
         s = _sketches(g["sketches"]) if len(g["sketches"]) else np.zeros((0, 16), dtype=np.uint64)
         d = np.ascontiguousarray(g.get("down", np.zeros(len(s))), dtype=np.uint64)
         o = np.ascontiguousarray(g.get("off", np.zeros(len(s) + 1)), dtype=np.uint64)
-        x = np.ascontiguousarray(g.get("ids", np.zeros(0, dtype=np.uint64)))
-        if x.dtype == np.uint32:
-            id_bytes = 4
-        else:
-            x = x.astype(np.uint64, copy=False)
+        x = np.ascontiguousarray(all_ids[i], dtype=id_dtype)
         keep += [s, d, o, x]
         sk[i], dn[i], of[i], ids[i] = _p(s), _p(d), _p(o), x.ctypes.data
     h = C.c_void_p()

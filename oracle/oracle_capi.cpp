@@ -382,7 +382,9 @@ std::vector<Dist> hnsw_search_bounded(const HNSWc& h, const Sketch& q, size_t k,
 
 int omp_threads_or_all(int t) {
 #ifdef _OPENMP
-  return t > 0 ? t : omp_get_max_threads();
+  // all logical CPUs this process may run on, like rayon's default pool (std::thread::available_parallelism);
+  // NOT omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1, which would time the baseline on one core
+  return t > 0 ? t : omp_get_num_procs();
 #else
   (void)t;
   return 1;
