@@ -5,12 +5,22 @@
   python bench.py --impl reference [...]                         the reference algorithm on the host cores (CPU oracle)
 
 Workload (BASELINE.json configs[1]): synthetic 10 M x 1024-bit sketches of laion2B-hammingv2 shape, 10 k queries,
-index built with m=24 M=256 efc=96, searched with ef=64 k=10.  A "step" is one Index::knns pass over the 10 k-query
-batch.  `value` has index and queries resident in HBM; `e2e` goes through the C-ABI hb_knns with pinned HOST buffers
-(H2D of the queries and D2H of ids/distances inside the timed region).  The index is built on the device by
-hb_build_hnsw (the reference cannot be compiled here, so there is no Rust-built .idx to load); both arms search an
-index built that way from the same data and parameters.  With N > 1 the index is replicated (built once per rank)
-and every rank searches its own 10 k-query batch: no data-path collective, weak scaling.
+index built with m=24 M=256 efc=96, searched with ef=64 k=10.  A "step" is one Index::knns pass over a 10 k-query
+batch.  `value` has index and queries resident in HBM; `e2e` goes through the C-ABI hb_knns with HOST buffers
+(pageable, what a Rust Vec<Sketch> is; the pinned figure is reported beside it), H2D of the queries and D2H of
+ids/distances inside the timed region.
+
+N > 1 (one process per GPU, launched by torchrun): rank 0 builds the index, the library replicates it GPU-to-GPU
+(hb_index_broadcast = ncclBroadcast inside libhnswb200), then
+  * `value`                 weak scaling: every rank searches its own 10 k batch, no data-path collective;
+  * `strong`                configs[2]: the ONE 10 k batch split N ways (contiguous slices, input order kept,
+                            src/index/mod.rs:36-41), the saturating 1 M batch split N ways, and the ef sweep 16..256
+                            (recall and QPS per ef) at that N;
+  * `ground_truth_sharded`  configs[3]: rows sharded N ways, hb_ground_truth_sharded_device (tcgen05 kernel ->
+                            ncclAllGather -> exact merge, all inside the library), ms + phase breakdown + a checksum
+                            that must be the same at every N;
+  * `sharded_hnsw_100M`     configs[4], N = 8 only: 8 shards x 12.5 M rows, per-shard device build, sharded search +
+                            all-gather + merge, recall against the sharded exact ground truth.
 
 Only the cpu_baseline / --impl reference legs touch oracle/ (CPU restatement of the reference), as the timed CPU
 baseline and as the checker of bit-exact parity; the product path never does.
@@ -18,6 +28,8 @@ baseline and as the checker of bit-exact parity; the product path never does.
 from __future__ import annotations
 
 import argparse
+import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
@@ -32,6 +44,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 METRIC = "queries/sec at recall@10>=0.93 (10Mx1024-bit, ef=64)"
+EF_SWEEP = [16, 24, 32, 48, 64, 96, 128, 192, 256]
 
 
 def parse():
@@ -49,6 +62,9 @@ def parse():
     ap.add_argument("--M", type=int, default=256)
     ap.add_argument("--rayon-threads", type=int, default=16, help="stands in for rayon's thread count at build time (chunk = 32x)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the strong / sweep / sharded legs (headline only)")
+    ap.add_argument("--no-100m", action="store_true", help="skip configs[4] (100 M sharded HNSW) at N = 8")
+    ap.add_argument("--shard-rows", type=int, default=12_500_000, help="rows per shard of configs[4]")
     return ap.parse_args()
 
 
@@ -95,9 +111,9 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def synth_on_device(hb, torch, n, seed):
+def synth_on_device(hb, torch, n, seed, start=0):
     t = torch.empty((n, 16), dtype=torch.int64, device="cuda")
-    hb.synth_sketches(t.data_ptr(), n, seed)
+    hb.synth_sketches(t.data_ptr(), n, seed, start=start)
     torch.cuda.synchronize()
     return t
 
@@ -116,6 +132,14 @@ def native_oracle():
     except Exception:
         path = orc.build()
     return orc, orc.Oracle(path)
+
+
+def host_threads() -> int:
+    """All logical CPUs this process may run on (rayon's default pool size); never OMP_NUM_THREADS, which torchrun sets to 1."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
 def oracle_index_from(idx, o):
@@ -138,7 +162,10 @@ def workload_name(a):
 
 
 def run_reference(a, rank, world):
-    """The reference algorithm on the host cores: oracle knns (OpenMP dynamic over queries ~ rayon par_iter, mod.rs:36-41)."""
+    """The reference algorithm on the host cores: oracle knns (OpenMP dynamic over queries ~ rayon par_iter, mod.rs:36-41)
+    with every logical CPU of the box, whatever OMP_NUM_THREADS says.  Rank 0 only; the index it searches is the one the
+    `ours` arm searches (built on the device by hb_build_hnsw from the same data and parameters -- the Rust builder cannot
+    run here; profiles/r02*_refbuilt*.json compares that graph with one from the restated CPU builder)."""
     if rank != 0:
         return
     import torch
@@ -149,106 +176,170 @@ def run_reference(a, rank, world):
     orc, o = native_oracle()
     oidx = oracle_index_from(idx, o)
     del idx
-    cores = o.max_threads()
+    cores = host_threads()
     for _ in range(a.warmup):
-        oidx.knns(q, a.k, a.ef)
+        oidx.knns(q, a.k, a.ef, threads=cores)
     t0 = time.perf_counter()
     for _ in range(a.steps):
-        oidx.knns(q, a.k, a.ef)
+        oidx.knns(q, a.k, a.ef, threads=cores)
     dt = time.perf_counter() - t0
     qps = a.nq * a.steps / dt
     line = {"impl": "reference", "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": dt / a.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64 xor+popcount",
-            "data": "synthetic", "config": {"workload": workload_name(a), "note": "CPU oracle (C++ restatement of the reference, -O3 -march=native, OpenMP) on rank 0 only"},
+            "data": "synthetic", "config": {"workload": workload_name(a), "note": f"CPU oracle (C++ restatement of the reference, -O3 -march=native, OpenMP, {cores} threads) on rank 0 only"},
             "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port",
                              "sample": f"the full {a.nq}-query batch, {a.steps} passes"},
             "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
+class Rig:
+    """Per-rank state of the `ours` arm: torch, the library, the communicator, and device-timing helpers."""
+
+    def __init__(self, a):
+        import torch
+        import torch.distributed as dist
+        import hnsw_itu_b200 as hb
+        from hnsw_itu_b200 import _lib
+        self.a, self.torch, self.dist, self.hb, self._lib = a, torch, dist, hb, _lib
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        torch.cuda.set_device(self.local_rank)
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+        self.lib = _lib.lib()
+        self.comm = hb.Comm.from_torch(self.local_rank)   # the library's own NCCL communicator (collectives run inside it)
+        self.stream = torch.cuda.current_stream().cuda_stream
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x: float) -> float:
+        if self.world == 1:
+            return x
+        t = self.torch.tensor([x], device="cuda", dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed(self, fn, steps: int, warmup: int = 3) -> float:
+        """ms per step: `warmup` untimed calls, then `steps` calls bracketed by barrier + synchronize, CUDA events on the
+        launching stream, max over ranks."""
+        torch = self.torch
+        for _ in range(warmup):
+            fn()
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = self.max_over_ranks(e0.elapsed_time(e1))
+        self.barrier()
+        return ms / steps
+
+    def knns_fn(self, h, dq, nq, k, ef, dk, dd, df, counters=None, q_off=0):
+        """A closure launching hb_knns_device on rows [q_off, q_off + nq) of dq into the same rows of dk/dd/df."""
+        lib, check, s = self.lib, self._lib.check, self.stream
+        qp, kp, dp, fp = dq.data_ptr() + q_off * 128, dk.data_ptr() + q_off * k * 8, dd.data_ptr() + q_off * k * 8, df.data_ptr() + q_off * 4
+        cp = counters.data_ptr() + q_off * 16 if counters is not None else None
+
+        def fn():
+            check(lib.hb_knns_device(h, qp, nq, k, ef, 0, kp, dp, fp, cp, s))
+        return fn
+
+    def gather_rows(self, t, q_off, nq):
+        """Every rank filled rows [q_off, q_off + nq) of its copy of t: sum the zero-padded copies into the full result."""
+        if self.world == 1:
+            return t
+        full = self.torch.zeros_like(t)
+        full[q_off:q_off + nq] = t[q_off:q_off + nq]
+        self.dist.all_reduce(full, op=self.dist.ReduceOp.SUM)
+        return full
+
+
+def split(n, world, r):
+    """Contiguous (start, len): the reference's `-b start -l len` (cli/src/main.rs:136-140)."""
+    e0, e1 = (r * n) // world, ((r + 1) * n) // world
+    return e0, e1 - e0
+
+
 def main():
     a = parse()
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
     if a.impl == "reference":
-        return run_reference(a, rank, world)
-
-    import torch
-    import torch.distributed as dist
-    import hnsw_itu_b200 as hb
-    from hnsw_itu_b200 import _lib
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    lib = _lib.lib()
+        return run_reference(a, int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
+    R = Rig(a)
+    torch, hb, lib, _lib = R.torch, R.hb, R.lib, R._lib
+    rank, world = R.rank, R.world
     want_cpu = (not a.no_cpu_baseline) and world == 1 and rank == 0
+    u64 = np.uint64
 
-    # ---- setup (untimed): data, index, queries, ground truth -------------------------------------------------
-    # N > 1: rank 0 builds the index once and its arrays are broadcast over NCCL/NVLink (replicated index); every rank
-    # then searches its own batch of nq queries with no data-path collective.
-    from hnsw_itu_b200 import sharded
-    dq = synth_on_device(hb, torch, a.nq, 1004 + rank)
-    idx, build_s, gt_keys, data, gt_ms, gt_e2e_ms = None, 0.0, None, None, None, None
+    # ---- setup (untimed): index on rank 0, replicated GPU-to-GPU by the library ---------------------------------
+    idx, build_s, data, gt_e2e_ms = None, 0.0, None, None
+    dq = synth_on_device(hb, torch, a.nq, 1004)                       # THE 10 k batch (configs[1]); same on every rank
+    dq_own = dq if rank == 0 else synth_on_device(hb, torch, a.nq, 1004 + rank)   # weak scaling: one batch per GPU
     if rank == 0:
         d_data, data, idx, build_s = build_index(hb, torch, a, keep_host=True)
-        # the same ground truth end to end through hb_ground_truth on HOST buffers (what the CLI's `ground-truth`
-        # calls): sliced upload overlapped with the search, results back on the host; wall clock, best of two after a warm-up
-        gt_e2e_ms = None
         if world == 1:
-            hq = dq.cpu().numpy().view(np.uint64)
+            # `ground-truth` end to end through hb_ground_truth on pageable HOST arrays (what the CLI calls): sliced upload
+            # overlapped with the search, results back on the host; wall clock, best of two after a warm-up
+            hq = dq.cpu().numpy().view(u64)
             for i in range(3):
                 t0 = time.perf_counter()
-                ek, _ = hb.ground_truth(data, hq, a.k)
+                hb.ground_truth(data, hq, a.k)
                 dt = (time.perf_counter() - t0) * 1e3
                 if i:
                     gt_e2e_ms = dt if gt_e2e_ms is None else min(gt_e2e_ms, dt)
         if not want_cpu:
-            del data
-        gt = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
-        # exact ground truth for the recall figure = BASELINE.json configs[3] on one GPU (the `ground-truth` path as a
-        # tcgen05 GEMM on E2M1 operands with fused top-k); timed here with CUDA events, best of the three calls after one
-        # warm-up call, reported beside the headline
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        gt_ms = None
-        for i in range(4):
-            g0.record()
-            _lib.check(lib.hb_ground_truth_device(d_data.data_ptr(), a.n, 0, dq.data_ptr(), a.nq, a.k, gt.data_ptr(), None))
-            g1.record()
-            torch.cuda.synchronize()
-            if i:
-                gt_ms = g0.elapsed_time(g1) if gt_ms is None else min(gt_ms, g0.elapsed_time(g1))
-        gt_keys = gt.cpu().numpy().view(np.uint64) & np.uint64(0xFFFFFFFF)
-        del d_data, gt
+            data = None
+        del d_data
         torch.cuda.empty_cache()
     t_b = time.time()
-    idx = sharded.broadcast_index(idx, src=0)
+    idx = R.comm.broadcast_index(idx, 0)     # hb_index_broadcast: ncclBroadcast of sketches / adjacency rows / down-links
+    R.barrier()
     bcast_s = time.time() - t_b
+    h = idx._h
+
+    # ---- configs[3]: exact ground truth with the rows sharded over the ranks (also the recall reference) -------
+    r0, rl = split(a.n, world, rank)
+    d_shard = synth_on_device(hb, torch, rl, 1003, start=r0)
+    d_gt = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
+
+    def gt_fn():
+        R.comm.ground_truth_sharded(d_shard.data_ptr(), rl, r0, dq.data_ptr(), a.nq, a.k, d_gt.data_ptr(), R.stream)
+    gt_ms = R.timed(gt_fn, 3, warmup=1)
+    gt_phase = R.comm.phase_ms()
+    gt_packed = d_gt.cpu().numpy().view(u64)
+    gt_keys = gt_packed & u64(0xFFFFFFFF)
+    gt_sha = hashlib.sha256(gt_packed.tobytes()).hexdigest()[:16]
+    del d_shard
+    torch.cuda.empty_cache()
+
     dk = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
     dd = torch.empty_like(dk)
     df = torch.empty(a.nq, dtype=torch.int32, device="cuda")
     dc = torch.empty((a.nq, 4), dtype=torch.int32, device="cuda")
-    stream = torch.cuda.current_stream().cuda_stream
-    h, qp, kp, dp, fp = idx._h, dq.data_ptr(), dk.data_ptr(), dd.data_ptr(), df.data_ptr()
 
-    def step():
-        _lib.check(lib.hb_knns_device(h, qp, a.nq, a.k, a.ef, 0, kp, dp, fp, None, stream))
-
-    _lib.check(lib.hb_knns_device(h, qp, a.nq, a.k, a.ef, 0, kp, dp, fp, dc.data_ptr(), stream))  # counted pass
-    gpu_keys = dk.cpu().numpy().view(np.uint64).copy()
-    gpu_dists = dd.cpu().numpy().view(np.uint64).copy()
-    ctr = dc.cpu().numpy().astype(np.float64)
-    recall = recall_at_k(gpu_keys, gt_keys, a.k) if rank == 0 else None
-
-    # ---- device-resident timing -------------------------------------------------------------------------------
-    for _ in range(max(a.warmup, 3)):
-        step()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    if world > 1:
-        dist.barrier()
+    # counted pass over the common batch: results for parity / recall, counters for the byte model
+    R.knns_fn(h, dq, a.nq, a.k, a.ef, dk, dd, df, counters=dc)()
     torch.cuda.synchronize()
+    gpu_keys = dk.cpu().numpy().view(u64).copy()
+    gpu_dists = dd.cpu().numpy().view(u64).copy()
+    ctr = dc.cpu().numpy().astype(np.float64)
+    recall = recall_at_k(gpu_keys, gt_keys, a.k)
+
+    # ---- headline: device-resident, one 10 k batch per GPU ------------------------------------------------------
+    step = R.knns_fn(h, dq_own, a.nq, a.k, a.ef, dk, dd, df)
+    warm = max(a.warmup, 3)
+    for _ in range(warm):
+        step()
+    sampler = ClockSampler(R.local_rank)
+    sampler.start()
+    R.barrier()
     launches0 = lib.hb_kernel_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kernel_ms = []
@@ -259,66 +350,160 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     launches = lib.hb_kernel_launches() - launches0
-    total_ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([total_ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
-        dist.barrier()
+    total_ms = R.max_over_ranks(e0.elapsed_time(e1))
+    R.barrier()
     clocks = sampler.stop()
 
-    # ---- end to end through the C ABI with pinned host buffers ----------------------------------------------
-    hq = torch.empty((a.nq, 16), dtype=torch.int64).pin_memory()
-    hq.copy_(dq.cpu())
-    hk = torch.empty((a.nq, a.k), dtype=torch.int64).pin_memory()
-    hd = torch.empty((a.nq, a.k), dtype=torch.int64).pin_memory()
-    hf = torch.empty(a.nq, dtype=torch.int32).pin_memory()
-    import ctypes as C
+    # ---- end to end through the C ABI with HOST buffers: pageable (the headline e2e) and pinned --------------------
     u64p, u32p = C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)
-    args = (h, C.cast(hq.data_ptr(), u64p), a.nq, a.k, a.ef, 0, C.cast(hk.data_ptr(), u64p), C.cast(hd.data_ptr(), u64p),
-            C.cast(hf.data_ptr(), u32p), None)
-    for _ in range(max(a.warmup, 3)):
-        _lib.check(lib.hb_knns(*args))
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(a.steps):
-        _lib.check(lib.hb_knns(*args))
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    assert np.array_equal(hk.numpy().view(np.uint64), gpu_keys), "host-buffer path returned different ids"
+
+    def e2e_leg(hq, hk, hd, hf):
+        args = (h, C.cast(hq.data_ptr(), u64p), a.nq, a.k, a.ef, 0, C.cast(hk.data_ptr(), u64p), C.cast(hd.data_ptr(), u64p),
+                C.cast(hf.data_ptr(), u32p), None)
+        for _ in range(warm):
+            _lib.check(lib.hb_knns(*args))
+        R.barrier()
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            _lib.check(lib.hb_knns(*args))
+        torch.cuda.synchronize()
+        return R.max_over_ranks(time.perf_counter() - t0)
+
+    host = dict(hq=dq_own.cpu(), hk=torch.empty((a.nq, a.k), dtype=torch.int64), hd=torch.empty((a.nq, a.k), dtype=torch.int64),
+                hf=torch.empty(a.nq, dtype=torch.int32))
+    e2e_pageable_s = e2e_leg(**host)
+    if rank == 0:
+        assert np.array_equal(host["hk"].numpy().view(u64), gpu_keys), "pageable host-buffer path returned different ids"
+    pinned = {k_: v.pin_memory() for k_, v in host.items()}
+    e2e_pinned_s = e2e_leg(**pinned)
+    if rank == 0:
+        assert np.array_equal(pinned["hk"].numpy().view(u64), gpu_keys), "pinned host-buffer path returned different ids"
+
+    extras = {}
+    if not a.no_extras:
+        extras = run_extras(R, a, idx, dq, gpu_keys, gt_keys)
 
     if rank != 0:
         if world > 1:
-            dist.destroy_process_group()
+            R.dist.destroy_process_group()
         return
+    report(R, a, idx, dict(build_s=build_s, bcast_s=bcast_s, data=data, gt_e2e_ms=gt_e2e_ms, gt_ms=gt_ms, gt_phase=gt_phase,
+                           gt_sha=gt_sha, gt_keys=gt_keys, gpu_keys=gpu_keys, gpu_dists=gpu_dists, ctr=ctr, recall=recall, kernel_ms=kernel_ms,
+                           total_ms=total_ms, launches=launches, clocks=clocks, e2e_pageable_s=e2e_pageable_s,
+                           e2e_pinned_s=e2e_pinned_s, warm=warm, want_cpu=want_cpu, dq=dq, extras=extras))
+    if world > 1:
+        R.dist.destroy_process_group()
+
+
+def run_extras(R, a, idx, dq, gpu_keys, gt_keys):
+    """configs[2] (split batch, saturating batch, ef sweep) and, at N = 8, configs[4] (100 M sharded HNSW)."""
+    torch, hb, world, rank = R.torch, R.hb, R.world, R.rank
+    u64 = np.uint64
+    h = idx._h
+    out = {}
+    # ---- the ONE 10 k batch split N ways: contiguous slices, outputs in input order ---------------------------
+    qs, ql = split(a.nq, world, rank)
+    dk = torch.zeros((a.nq, a.k), dtype=torch.int64, device="cuda")
+    dd = torch.zeros_like(dk)
+    df = torch.zeros(a.nq, dtype=torch.int32, device="cuda")
+    fn = R.knns_fn(h, dq, ql, a.k, a.ef, dk, dd, df, q_off=qs)
+    ms = R.timed(fn, a.steps)
+    same = bool(np.array_equal(R.gather_rows(dk, qs, ql).cpu().numpy().view(u64), gpu_keys))
+    out["split_10k"] = {"queries": a.nq, "queries_per_gpu": ql, "ms_per_batch": ms, "qps": a.nq / ms * 1e3,
+                        "identical_to_unsplit_ids": same,
+                        "note": "one launch per GPU over its contiguous slice; below one wave per GPU the limiter is the per-query "
+                                "dependent chain, not a collective (there is none)"}
+    # ---- saturating batch: the 10 k queries tiled x100 = 1 M, split N ways ------------------------------------
+    tile = 100
+    nq_sat = a.nq * tile
+    ss, sl = split(nq_sat, world, rank)
+    dq_sat = dq.repeat(tile, 1)[ss:ss + sl].contiguous()
+    sk = torch.empty((sl, a.k), dtype=torch.int64, device="cuda")
+    sd = torch.empty_like(sk)
+    sf = torch.empty(sl, dtype=torch.int32, device="cuda")
+    ms = R.timed(R.knns_fn(h, dq_sat, sl, a.k, a.ef, sk, sd, sf), 3, warmup=1)
+    out["saturating_1M"] = {"queries": nq_sat, "queries_per_gpu": sl, "ms_per_batch": ms, "qps": nq_sat / ms * 1e3}
+    # ---- ef sweep: recall and QPS per ef on the split 10 k batch and on the saturating batch -------------------
+    sweep = []
+    for ef in EF_SWEEP:
+        ms10 = R.timed(R.knns_fn(h, dq, ql, a.k, ef, dk, dd, df, q_off=qs), 3, warmup=1)
+        keys = R.gather_rows(dk, qs, ql).cpu().numpy().view(u64)
+        mssat = R.timed(R.knns_fn(h, dq_sat, sl, a.k, ef, sk, sd, sf), 2, warmup=1)
+        sweep.append({"ef": ef, "recall_at_10": recall_at_k(keys, gt_keys, a.k), "qps_split_10k": a.nq / ms10 * 1e3,
+                      "qps_saturating_1M": nq_sat / mssat * 1e3})
+    out["ef_sweep"] = sweep
+    del dq_sat, sk, sd, sf
+    torch.cuda.empty_cache()
+
+    # ---- configs[4]: 100 M rows as N shards, one HNSW per shard, sharded search + all-gather + exact merge ------
+    if world == 8 and not a.no_100m:
+        rows = a.shard_rows
+        off = rank * rows
+        d_shard = synth_on_device(hb, torch, rows, 1003, start=off)
+        t0 = time.time()
+        sidx = hb.build_hnsw(d_shard.cpu().numpy().view(u64), efc=a.efc, m=a.m, M=a.M, rayon_threads=a.rayon_threads, keep_host=False)
+        R.barrier()
+        build_s = time.time() - t0
+        d_gt = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
+        gt_fn = lambda: R.comm.ground_truth_sharded(d_shard.data_ptr(), rows, off, dq.data_ptr(), a.nq, a.k, d_gt.data_ptr(), R.stream)  # noqa: E731
+        gt_ms = R.timed(gt_fn, 2, warmup=1)
+        gt_phase = R.comm.phase_ms()
+        gt100 = d_gt.cpu().numpy().view(u64) & u64(0xFFFFFFFF)
+        d_out = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
+        fn = lambda: R.comm.knns_sharded(sidx, off, dq.data_ptr(), a.nq, a.k, a.ef, d_out.data_ptr(), R.stream)  # noqa: E731
+        ms = R.timed(fn, 5, warmup=2)
+        ph = R.comm.phase_ms()
+        keys = d_out.cpu().numpy().view(u64) & u64(0xFFFFFFFF)
+        out["sharded_hnsw_100M"] = {
+            "rows": rows * world, "shards": world, "per_shard_build_s": build_s, "ms_per_batch": ms, "qps": a.nq / ms * 1e3,
+            "recall_at_10": recall_at_k(keys, gt100, a.k), "ef": a.ef,
+            "phase_ms_rank0": {"search": ph[0], "all_gather": ph[1], "merge": ph[2]},
+            "ground_truth_100M": {"ms": gt_ms, "phase_ms_rank0": {"search": gt_phase[0], "all_gather": gt_phase[1], "merge": gt_phase[2]},
+                                  "pairs_per_s": a.nq * rows * world / (gt_ms * 1e-3)},
+            "note": "every rank searches all queries on its shard (the reference's `index -b -l` sub-range), local keys + offset, "
+                    "ncclAllGather of nq*k packed u64 per rank + exact (distance, key) merge inside libhnswb200"}
+        del sidx, d_shard
+        torch.cuda.empty_cache()
+    return out
+
+
+def report(R, a, idx, s):
+    """Rank 0: CPU baseline + parity (N = 1), roofline, the JSON line."""
+    world = R.world
+    u64 = np.uint64
+    ctr, gpu_keys, gpu_dists = s["ctr"], s["gpu_keys"], s["gpu_dists"]
+    cores = host_threads()
 
     # ---- CPU baseline + parity (rank 0, N = 1): the oracle on the same index, all host threads -----------------
-    cpu, parity, v_alg = None, None, None
-    if want_cpu:
+    cpu, parity, v_alg, gt_cpu = None, None, None, None
+    q = s["dq"].cpu().numpy().view(u64)
+    if s["want_cpu"]:
         orc, o = native_oracle()
         oidx = oracle_index_from(idx, o)
-        q = dq.cpu().numpy().view(np.uint64)
-        ok, od, of, oc = oidx.knns(q, a.k, a.ef, counters=True)
+        ok, od, of, oc = oidx.knns(q, a.k, a.ef, counters=True, threads=cores)
         same = int(((ok == gpu_keys).all(axis=1) & (od == gpu_dists).all(axis=1)).sum())
-        xea = bool(np.array_equal(oc[:, [0, 1, 3]], ctr[:, [0, 1, 3]].astype(np.uint64)))
+        xea = bool(np.array_equal(oc[:, [0, 1, 3]], ctr[:, [0, 1, 3]].astype(u64)))
         parity = {"queries_identical_ids_and_distances": same, "of": a.nq, "expansion_counters_identical": xea}
         v_alg = float(oc[:, 2].mean())
         best = 1e30
         for _ in range(3):
             t0 = time.perf_counter()
-            oidx.knns(q, a.k, a.ef)
+            oidx.knns(q, a.k, a.ef, threads=cores)
             best = min(best, time.perf_counter() - t0)
         t0 = time.perf_counter()
         oidx.knns(q[:1000], a.k, a.ef, threads=1)
         t1 = time.perf_counter() - t0
-        cpu = {"value": a.nq / best, "unit": "queries/s", "cores": o.max_threads(), "kind": "port",
+        cpu = {"value": a.nq / best, "unit": "queries/s", "cores": cores, "kind": "port",
                "sample": f"the full {a.nq}-query batch on the same index, best of 3; 1 thread: {1000 / t1:.0f} queries/s on 1000 queries"}
+        # ground truth on the CPU: oracle Bruteforce (per-query full scan + min_k, bruteforce.rs:37-47) on a bounded sample
+        ns = min(1000, a.nq)
+        t0 = time.perf_counter()
+        ck, cd = o.ground_truth(s["data"], q[:ns], a.k, threads=cores)
+        tg = time.perf_counter() - t0
+        gt_cpu = {"value": ns * a.n / tg, "unit": "pairs/s", "cores": cores, "kind": "port",
+                  "sample": f"{ns} of the {a.nq} queries x all {a.n} rows in {tg:.2f} s; the full batch scales linearly: {tg * a.nq / ns:.1f} s",
+                  "ids_identical_to_gpu_on_sample": bool(np.array_equal(ck, s["gt_keys"][:ns]))}
+        del oidx
 
     # ---- roofline of the search kernel: algorithmic gather bytes / kernel time --------------------------------
     X, E, Vgpu = ctr[:, 0].mean(), ctr[:, 1].mean(), ctr[:, 2].mean()
@@ -330,14 +515,14 @@ def main():
             orc, o = native_oracle()
             oidx = oracle_index_from(idx, o)
             ns = min(500, a.nq)
-            _, _, _, oc = oidx.knns(dq.cpu().numpy().view(np.uint64)[:ns], a.k, a.ef, counters=True)
+            _, _, _, oc = oidx.knns(q[:ns], a.k, a.ef, counters=True, threads=cores)
             v_alg = float(oc[:, 2].mean()) * float(Vgpu / ctr[:ns, 2].mean())
             v_note = f"oracle |visited| on the first {ns} queries, scaled to the batch by the GPU's evaluation counts"
         except Exception as e:  # host graphs not kept: fall back to the GPU's (larger) count and say so
             v_note = f"GPU distance evaluations (oracle sample unavailable: {type(e).__name__}); overstates the algorithmic bytes"
     V = v_alg if v_alg is not None else Vgpu
     bytes_q = 128 * V + 4 * E + 8 * X + 128 + 16 * a.k
-    k_ms = float(np.mean(kernel_ms))
+    k_ms = float(np.mean(s["kernel_ms"]))
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -345,51 +530,54 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = bytes_q * a.nq / (k_ms * 1e-3) / 1e9
-    traffic = None
+    traffic, kname = None, "hnsw_search_v2_kernel<2, true, false>"
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "search_kernel_ncu.json"))).get("dram_bytes_per_launch")
+        prof = json.load(open(os.path.join(ROOT, "profiles", "search_kernel_ncu.json")))
+        traffic = prof.get("dram_bytes_per_launch")
     except Exception:
         pass
+    total_ms, e2e_s, e2e_pin_s = s["total_ms"], s["e2e_pageable_s"], s["e2e_pinned_s"]
     value = world * a.nq * a.steps / (total_ms * 1e-3)
+    gt_ms, gt_phase = s["gt_ms"], s["gt_phase"]
+    ops = 2.0 * a.nq * a.n * 1024
+    tops = ops / (gt_ms * 1e-3) / 1e12
     line = {
-        "metric": METRIC, "value": value, "unit": "queries/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+        "metric": METRIC, "value": value, "unit": "queries/s", "n_gpus": world, "steps": a.steps, "warmup": s["warm"],
         "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64 xor+popcount (integer exact)", "data": "synthetic",
-        "config": {"workload": workload_name(a), "recall_at_10": recall, "l2": "inputs larger than L2: the index is "
+        "config": {"workload": workload_name(a), "recall_at_10": s["recall"], "l2": "inputs larger than L2: the index is "
                    f"{idx.info().device_bytes / 1e9:.1f} GB and one step gathers {bytes_q * a.nq / 1e9:.2f} GB",
-                   "index_build_s": build_s, "index_broadcast_s": bcast_s if world > 1 else None, "parallelism": "replicated index (built on rank 0, broadcast over NCCL), one query batch per GPU, no data-path collective" if world > 1 else "1 GPU",
+                   "index_build_s": s["build_s"], "index_broadcast_s": s["bcast_s"] if world > 1 else None,
+                   "parallelism": ("replicated index (built on rank 0, replicated GPU-to-GPU by hb_index_broadcast = ncclBroadcast inside the "
+                                   "library), one query batch per GPU, no data-path collective") if world > 1 else "1 GPU",
+                   "host_cores": cores,
                    "per_query": {"expansions": X, "ids_scanned": E, "visited_reference": V, "visited_reference_source": v_note,
                                  "distance_evals_gpu": Vgpu}},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "kernel": "hnsw_search_fast_kernel<2>", "kernel_ms": k_ms, "bytes_per_query": bytes_q,
+                     "kernel": kname, "kernel_ms": k_ms, "bytes_per_query": bytes_q,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
         "cpu_baseline": cpu,
         "e2e": {"value": world * a.nq * a.steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": a.nq * 128,
                 "d2h_bytes_per_step": a.nq * a.k * 16 + a.nq * 4, "ms_per_step": e2e_s / a.steps * 1e3,
-                "how": "hb_knns on pinned host buffers: queries are read from and results written to host memory across PCIe "
-                       "inside the timed region (the search kernel accesses the mapped buffers in place; pageable buffers are staged with cudaMemcpyAsync)"},
-        "gpu_launches": int(launches), "clocks": clocks, "parity": parity,
+                "how": "hb_knns on PAGEABLE host buffers (a Rust Vec<Sketch> / numpy array): cudaMemcpyAsync of the queries to a pooled "
+                       "staging set, search, cudaMemcpyAsync of keys / distances / found back, all inside the timed region",
+                "pinned": {"value": world * a.nq * a.steps / e2e_pin_s, "ms_per_step": e2e_pin_s / a.steps * 1e3,
+                           "how": "same call on page-locked buffers: the kernel reads queries from and writes results to mapped host memory in place"}},
+        "gpu_launches": int(s["launches"]), "clocks": s["clocks"], "parity": parity,
+        "ground_truth_sharded": {
+            "workload": f"brute-force Hamming top-{a.k}, {a.n} x {a.nq} (BASELINE.json configs[3]), rows sharded over {world} GPU(s)",
+            "ms": gt_ms, "pairs_per_s": a.nq * a.n / (gt_ms * 1e-3), "checksum_sha256_16": s["gt_sha"],
+            "phase_ms_rank0": {"search": gt_phase[0], "all_gather": gt_phase[1], "merge": gt_phase[2]},
+            "how": "hb_ground_truth_sharded_device on every rank: tcgen05 E2M1 GEMM + fused top-k over the rank's rows, ncclAllGather of "
+                   "nq*k packed (distance << 32 | key), exact merge kernel -- all inside libhnswb200; mean of 3 calls, max over ranks; "
+                   "the checksum (sha256 of the packed result) is the same at every N",
+            "e2e_host_buffers_ms": s["gt_e2e_ms"], "cpu_baseline": gt_cpu,
+            "roofline": {"bound": "tensor", "achieved": tops, "unit": "Top/s on 4-bit operands (2*nq*N*1024 per call, whole job)",
+                         "peak": 9000.0 * world, "frac": tops / (9000.0 * world),
+                         "peak_source": "nominal dense fp4 9000 Top/s per GPU (MEASURED_PEAKS.json has no fp4 figure; of nominal)"}},
     }
-    if gt_ms is not None:
-        ops = 2.0 * a.nq * a.n * 1024
-        tops = ops / (gt_ms * 1e-3) / 1e12
-        bf16 = float(peaks.get("bf16_tflops", 1590.0))
-        mma = a.nq >= 32 and a.n >= 4096
-        line["ground_truth"] = {
-            "workload": f"brute-force Hamming top-{a.k}, {a.n} x {a.nq} (BASELINE.json configs[3] on one GPU), untimed setup of the headline",
-            "kernel": "gt_mxf4_kernel (tcgen05.mma kind::mxf4.block_scale on E2M1 operands with unit scales, TMEM accumulators, fused top-k)" if mma else "scan_topk_kernel",
-            "ms": gt_ms, "pairs_per_s": a.nq * a.n / (gt_ms * 1e-3),
-            "e2e_host_buffers_ms": gt_e2e_ms, "e2e_note": "hb_ground_truth on pageable host arrays: upload of the rows in slices by "
-            "host threads through page-locked slots, overlapped with the search of the previous slice, results copied back; wall clock",
-            "roofline": {"bound": "tensor", "achieved": tops, "unit": "Top/s on 4-bit operands (2*nq*N*1024 per call)",
-                         "peak": 4.0 * bf16, "frac": tops / (4.0 * bf16),
-                         "peak_source": "4 x MEASURED_PEAKS.json bf16_tflops (no fp4 figure is measured; nominal dense fp4 is 9000, int8 4500)",
-                         "frac_of_nominal_9000": tops / 9000.0,
-                         "note": "tensor pipe 80 % active in the ncu capture (profiles/r01k_gt_mxf4_kernel_ncu_summary.json); the rest is the "
-                                 "epilogue at the TMEM read rate and the operand expansion sharing issue slots (DESIGN.md 4.3)"}}
+    line.update({"strong": s["extras"]} if s["extras"] else {})
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -12,3 +12,4 @@ compiled in this environment, so the mirror is Python over the C ABI):
 """
 from .index import (Distance, Index, Sketch, build_hnsw, ground_truth, index_from_parts, read_index, synth_sketches)  # noqa: F401
 from ._lib import HbError, build_library  # noqa: F401
+from .multi import Comm, MultiIndex  # noqa: F401,E402

@@ -101,6 +101,31 @@ def lib() -> C.CDLL:
     L.hb_pack_device.argtypes = [vp, vp, vp, C.c_uint64, C.c_uint32, C.c_uint64, vp, vp]
     L.hb_synth_device.argtypes = [C.POINTER(SynthParamsC), C.c_uint64, C.c_uint64, vp, vp]
     L.hb_build_hnsw.argtypes = [_u64p, C.c_uint64, C.POINTER(BuildParamsC), C.c_int, C.c_int, C.POINTER(vp)]
+    # multi-GPU (multi.cu)
+    u8p, dbl3 = C.POINTER(C.c_uint8), C.POINTER(C.c_double)
+    L.hb_comm_unique_id.argtypes = [u8p]
+    L.hb_comm_init_rank.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    L.hb_comm_free.argtypes = [vp]
+    L.hb_comm_free.restype = None
+    L.hb_comm_phase_ms.argtypes = [vp, dbl3]
+    L.hb_ground_truth_sharded_device.argtypes = [vp, vp, C.c_uint64, C.c_uint64, vp, C.c_uint64, C.c_uint32, vp, vp]
+    L.hb_knns_sharded_device.argtypes = [vp, vp, C.c_uint64, vp, C.c_uint64, C.c_uint32, C.c_uint32, vp, vp]
+    L.hb_index_broadcast.argtypes = [vp, vp, C.c_int, C.POINTER(vp)]
+    L.hb_multi_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
+    L.hb_multi_free.argtypes = [vp]
+    L.hb_multi_free.restype = None
+    L.hb_multi_device_count.argtypes = [vp]
+    L.hb_multi_size.argtypes = [vp]
+    L.hb_multi_size.restype = C.c_uint64
+    L.hb_multi_load_idx.argtypes = [vp, C.c_char_p]
+    L.hb_multi_replicate.argtypes = [vp, vp]
+    L.hb_multi_build_sharded.argtypes = [vp, _u64p, C.c_uint64, C.POINTER(BuildParamsC)]
+    L.hb_multi_load_shards.argtypes = [vp, C.POINTER(C.c_char_p), _u64p]
+    L.hb_multi_knns.argtypes = [vp, _u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, _u64p, _u64p, _u32p]
+    L.hb_multi_ground_truth.argtypes = [vp, _u64p, C.c_uint64, _u64p, C.c_uint64, C.c_uint32, _u64p, _u64p]
+    L.hb_multi_phase_ms.argtypes = [vp, dbl3]
+    L.hb_multi_index.argtypes = [vp, C.c_int]
+    L.hb_multi_index.restype = vp
     _lib = L
     return L
 

@@ -23,26 +23,6 @@ void count_launches(uint64_t n) { g_launches.fetch_add(n, std::memory_order_rela
 
 namespace {
 
-template <class F>
-int guarded(F&& f) {
-  try {
-    f();
-    return HB_OK;
-  } catch (const Error& e) {
-    g_last_error = e.what();
-    return e.code;
-  } catch (const std::bad_alloc&) {
-    g_last_error = "host allocation failed";
-    return HB_ERR_OOM;
-  } catch (const std::exception& e) {
-    g_last_error = e.what();
-    return HB_ERR_INTERNAL;
-  } catch (...) {
-    g_last_error = "unknown error";
-    return HB_ERR_INTERNAL;
-  }
-}
-
 template <class T>
 struct DevMem {
   T* p = nullptr;

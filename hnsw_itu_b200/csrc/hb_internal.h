@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <memory>
 #include <mutex>
 #include <stdexcept>
 #include <string>
@@ -36,6 +37,27 @@ void count_launches(uint64_t n = 1);  // every kernel launch of the library is c
     if (!(cond)) throw hb::Error((code), (msg)); \
   } while (0)
 
+// every extern "C" entry point runs its body through this: exceptions become hb_status codes + hb_last_error()
+template <class F>
+int guarded(F&& f) {
+  try {
+    f();
+    return HB_OK;
+  } catch (const Error& e) {
+    set_last_error(e.what());
+    return e.code;
+  } catch (const std::bad_alloc&) {
+    set_last_error("host allocation failed");
+    return HB_ERR_OOM;
+  } catch (const std::exception& e) {
+    set_last_error(e.what());
+    return HB_ERR_INTERNAL;
+  } catch (...) {
+    set_last_error("unknown error");
+    return HB_ERR_INTERNAL;
+  }
+}
+
 // ---- host-side graph arrays (one per graph; graph 0 = base) -----------------
 struct HostGraph {
   uint64_t n = 0;
@@ -55,7 +77,9 @@ struct Attrs {
   std::string params;
 };
 
-// per-device scratch of the search kernel, cached on the index
+// scratch of ONE search call (control words, retry maps, the exact visited tables of the large-capacity kernel, timing
+// events).  Pooled on the index: concurrent hb_knns* calls each take their own, so nothing serialises them
+// (Index::search is callable from any thread, src/index/mod.rs:21-43).
 struct SearchWorkspace {
   uint32_t vcap_log2 = 0;  // visited-table capacity per warp slot (log2, 32-bit words)
   uint32_t slots = 0;      // resident warp slots the tables were sized for
@@ -66,6 +90,8 @@ struct SearchWorkspace {
   uint32_t* qstatus = nullptr; // per query (capacity qcap)
   uint32_t* qmap = nullptr;    // retry indirection (capacity qcap)
   uint64_t qcap = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  ~SearchWorkspace();
 };
 
 // device staging of one hb_knns call with host buffers (pooled on the index: no cudaMalloc on the hot path)
@@ -98,12 +124,10 @@ struct Index {
   uint64_t device_bytes = 0;
   int sm_count = 0;
   uint64_t build_dropped_appends = 0, build_prunes = 0, build_unlinked = 0;  // builder.cu statistics
-  mutable std::mutex mu;  // serialises launches that share the workspace
   mutable std::mutex pool_mu;
   mutable std::vector<CallBuffers> pool;  // idle staging sets
-  mutable cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  mutable double last_search_ms = 0.0;  // device time of the search kernel(s) of the last knns call on this index
-  mutable SearchWorkspace ws;
+  mutable std::vector<std::unique_ptr<SearchWorkspace>> ws_pool;  // idle search workspaces (guarded by pool_mu)
+  mutable double last_search_ms = 0.0;  // device time of the search kernel(s) of the last completed knns call on this index
   ~Index();
 };
 
@@ -144,6 +168,9 @@ void pack_device(const void* d_keys, const void* d_dists, const void* d_found, u
 
 // synth.cu
 void synth_device(const hb_synth_params& p, uint64_t start, uint64_t n, void* d_out, cudaStream_t stream);
+
+// multi.cu
+struct Comm;
 
 // builder.cu
 Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& p, int device, bool keep_host);

@@ -88,15 +88,19 @@ Index::~Index() {
   cudaFree(d_sk);
   cudaFree(d_adj);
   cudaFree(d_down);
-  cudaFree(ws.vis);
-  cudaFree(ws.spill);
-  cudaFree(ws.ctl);
-  cudaFree(ws.qstatus);
-  cudaFree(ws.qmap);
+  ws_pool.clear();
   for (CallBuffers& b : pool) {
     cudaFree(b.q); cudaFree(b.keys); cudaFree(b.dists); cudaFree(b.found); cudaFree(b.ctr);
     if (b.stream) cudaStreamDestroy(b.stream);
   }
+}
+
+SearchWorkspace::~SearchWorkspace() {
+  cudaFree(vis);
+  cudaFree(spill);
+  cudaFree(ctl);
+  cudaFree(qstatus);
+  cudaFree(qmap);
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
 }

@@ -34,6 +34,7 @@
 #include <memory>
 
 #include "beam.cuh"
+#include "beam2.cuh"
 #include "hb_internal.h"
 
 namespace hb {
@@ -411,16 +412,149 @@ FastLaunch fast_kernel_for(uint32_t ef) {
   return {hnsw_search_fast_kernel<8>};
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Fast path, second generation (beam2.cuh): split 32-bit beam registers, register gather with 4 lanes per sketch row,
+// recently-seen cache with 16-bit tags.  Same persistent-warp structure and the same results as the kernel above.
+// ---------------------------------------------------------------------------------------------
+#ifndef HB_MB2
+#define HB_MB2 8
+#endif
+#define HB_MIN_BLOCKS2(R) ((R) <= 2 ? HB_MB2 : (HB_MB2 < 7 ? HB_MB2 : 7))
+// entries (log2) of the recently-seen cache per warp: compile-time so that every shared-memory address folds
+#ifndef HB_CACHE2_LOG2
+#define HB_CACHE2_LOG2 11
+#endif
+template <bool TAG16>
+__host__ __device__ constexpr uint32_t cache2_log2() { return TAG16 ? HB_CACHE2_LOG2 : HB_CACHE2_LOG2 - 1; }  // same bytes either way
+
+template <int R, bool TAG16, bool COUNT>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS2(R)) hnsw_search_v2_kernel(const SearchParams p, uint32_t) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr uint32_t cache_log2 = cache2_log2<TAG16>();
+  const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  unsigned char* mine = smem_raw + wib * warp_scratch2_bytes<TAG16>(cache_log2);
+  WarpScratch2<TAG16> ws;
+  ws.stage = reinterpret_cast<uint4*>(mine);
+  ws.ids = reinterpret_cast<uint32_t*>(mine + kStageBytes2);
+  ws.spill = ws.ids + kIdsWords2;
+  unsigned char* const cache_mem = mine + kStageBytes2 + (kIdsWords2 + kSpillCap2) * 4;
+  ws.cache.init(cache_mem, cache_log2);
+  const GraphView gv{p.sk, p.adj, p.stride};
+
+  for (;;) {
+    uint32_t qi = 0;
+    if (lane == 0) qi = atomicAdd(p.ctl, 1u);
+    qi = __shfl_sync(kFullMask, qi, 0);
+    if (qi >= p.nq) break;
+    const uint32_t q = p.qmap ? p.qmap[qi] : qi;
+    const QueryRegs qr = load_query(p.queries, q);
+#ifdef HB_DIAG_TIME
+    unsigned long long t_start;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+#endif
+    fill_ff(cache_mem, SeenCache<TAG16>::bytes(cache_log2));
+
+    SearchCounters c;
+    uint32_t status = 0;
+    uint32_t cur = p.ep_gid;
+    BeamSplit<R> b;
+    for (int g = (int)p.n_upper; g >= 0 && status == 0; --g) {
+      const uint32_t ef = (g == 0) ? p.ef : 1u;  // hnsw.rs:286 (ef = 1 above the base)
+      beam_search2<R, TAG16, COUNT>(gv, qr, ef, cur, ws, b, c, status);
+      b.sort_prefix(g > 0 ? 1u : p.k);  // pop_min() above the base, drain_asc().take(k) at the base
+      if (g > 0 && status == 0) {
+        uint32_t d0, k0;
+        b.at(0, d0, k0);
+        cur = __ldg(p.down + (k0 - p.n_base));  // hnsw.rs:288-292 (.point.1)
+      }
+    }
+
+    // ---- drain_asc().take(k) (+ Indexes::search padding) ----
+    const uint32_t nres = status ? 0u : min(b.size, p.k);
+    uint32_t fd, fk;
+    b.at(0, fd, fk);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint32_t j = b.sorted_index(r);
+      if (j < nres) {
+        p.keys[(size_t)q * p.k + j] = b.wk[r];
+        p.dists[(size_t)q * p.k + j] = b.wd[r];
+      }
+    }
+    for (uint32_t j = nres + lane; j < p.k; j += 32) {
+      const bool pad = (p.flags & HB_PAD_LIKE_CLI) && nres;
+      p.keys[(size_t)q * p.k + j] = pad ? fk : 0;
+      p.dists[(size_t)q * p.k + j] = pad ? fd : 0;
+    }
+    if (lane == 0) {
+      p.found[q] = nres;
+      p.qstatus[q] = status;
+      if (status) atomicOr(p.ctl + 1, 1u);
+#ifdef HB_DIAG_TIME
+      unsigned long long t_end;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+      if (p.counters) p.counters[q] = make_uint4((uint32_t)t_start, (uint32_t)t_end, blockIdx.x * kWarpsPerBlock + wib, c.X);
+#else
+      if (COUNT) p.counters[q] = make_uint4(c.X, c.E, c.V, c.A);
+#endif
+    }
+    __syncwarp();
+  }
+}
+
+template <bool TAG16, bool COUNT>
+FastLaunch v2_kernel_for(uint32_t ef) {
+  FastLaunch fl;
+  if (ef <= 32) fl.kernel = hnsw_search_v2_kernel<1, TAG16, COUNT>;
+  else if (ef <= 64) fl.kernel = hnsw_search_v2_kernel<2, TAG16, COUNT>;
+  else if (ef <= 128) fl.kernel = hnsw_search_v2_kernel<4, TAG16, COUNT>;
+  else fl.kernel = hnsw_search_v2_kernel<8, TAG16, COUNT>;
+  return fl;
+}
+
 uint32_t ceil_log2(uint64_t x) {
   uint32_t l = 0;
   while ((1ull << l) < x) ++l;
   return l;
 }
 
-void ensure_common(const Index& idx, uint64_t nq);
+// ---- per-call workspace (pooled on the index) ---------------------------------------------------------------------
+struct WorkspaceLease {
+  const Index& idx;
+  std::unique_ptr<SearchWorkspace> ws;
+  explicit WorkspaceLease(const Index& i) : idx(i) {
+    {
+      std::lock_guard<std::mutex> lock(idx.pool_mu);
+      if (!idx.ws_pool.empty()) {
+        ws = std::move(idx.ws_pool.back());
+        idx.ws_pool.pop_back();
+      }
+    }
+    if (!ws) ws.reset(new SearchWorkspace());
+  }
+  ~WorkspaceLease() {
+    std::lock_guard<std::mutex> lock(idx.pool_mu);
+    idx.ws_pool.push_back(std::move(ws));
+  }
+};
 
-void ensure_workspace(const Index& idx, uint32_t vcap_log2, uint32_t slots, uint64_t nq, cudaStream_t stream) {
-  SearchWorkspace& ws = idx.ws;
+void ensure_common(SearchWorkspace& ws, uint64_t nq) {
+  if (!ws.ctl) HB_CUDA(cudaMalloc(&ws.ctl, 8 * sizeof(uint32_t)));
+  if (!ws.ev0) HB_CUDA(cudaEventCreate(&ws.ev0));
+  if (!ws.ev1) HB_CUDA(cudaEventCreate(&ws.ev1));
+  if (ws.qcap < nq) {
+    cudaFree(ws.qstatus);
+    cudaFree(ws.qmap);
+    ws.qstatus = ws.qmap = nullptr;
+    ws.qcap = 0;
+    HB_CUDA(cudaMalloc(&ws.qstatus, nq * 4));
+    HB_CUDA(cudaMalloc(&ws.qmap, nq * 4));
+    ws.qcap = nq;
+  }
+}
+
+void ensure_tables(SearchWorkspace& ws, uint32_t vcap_log2, uint32_t slots, uint64_t nq, cudaStream_t stream) {
   if (ws.vcap_log2 != vcap_log2 || ws.slots < slots) {
     cudaFree(ws.vis);
     cudaFree(ws.spill);
@@ -436,23 +570,44 @@ void ensure_workspace(const Index& idx, uint32_t vcap_log2, uint32_t slots, uint
     ws.vcap_log2 = vcap_log2;
     ws.slots = slots;
   }
-  ensure_common(idx, nq);
+  ensure_common(ws, nq);
 }
 
-void ensure_common(const Index& idx, uint64_t nq) {
-  SearchWorkspace& ws = idx.ws;
-  if (!ws.ctl) HB_CUDA(cudaMalloc(&ws.ctl, 8 * sizeof(uint32_t)));
-  if (!idx.ev0) HB_CUDA(cudaEventCreate(&idx.ev0));
-  if (!idx.ev1) HB_CUDA(cudaEventCreate(&idx.ev1));
-  if (ws.qcap < nq) {
-    cudaFree(ws.qstatus);
-    cudaFree(ws.qmap);
-    ws.qstatus = ws.qmap = nullptr;
-    ws.qcap = 0;
-    HB_CUDA(cudaMalloc(&ws.qstatus, nq * 4));
-    HB_CUDA(cudaMalloc(&ws.qmap, nq * 4));
-    ws.qcap = nq;
+// one launch on `stream`, timed with the workspace's events; returns after the stream has drained, h_ctl filled
+template <class Launch>
+double timed_launch(SearchWorkspace& ws, cudaStream_t stream, uint32_t* h_ctl, size_t n_ctl, Launch&& launch) {
+  HB_CUDA(cudaMemsetAsync(ws.ctl, 0, 8 * sizeof(uint32_t), stream));
+  HB_CUDA(cudaEventRecord(ws.ev0, stream));
+  launch();
+  count_launches();
+  HB_CUDA(cudaGetLastError());
+  HB_CUDA(cudaEventRecord(ws.ev1, stream));
+  HB_CUDA(cudaMemcpyAsync(h_ctl, ws.ctl, n_ctl * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  HB_CUDA(cudaStreamSynchronize(stream));
+  float ms = 0.f;
+  HB_CUDA(cudaEventElapsedTime(&ms, ws.ev0, ws.ev1));
+  return ms;
+}
+
+struct FastChoice {
+  FastLaunch fl;
+  size_t smem;
+};
+// which ef <= 256 kernel serves this index: the v2 kernel with 16-bit cache tags while they are exact for n_total,
+// with full ids above; HB_SEARCH_V1=1 selects the round-1 kernel (kept for A/B timing)
+FastChoice choose_fast(const Index& idx, uint32_t ef, bool count, uint32_t& cache_log2) {
+  static const bool v1 = std::getenv("HB_SEARCH_V1") != nullptr;
+  if (v1) {
+    static const int env_cache = std::getenv("HB_CACHE_LOG2") ? std::atoi(std::getenv("HB_CACHE_LOG2")) : 0;
+    cache_log2 = env_cache >= 5 && env_cache <= 13 ? (uint32_t)env_cache : 9u;
+    return {fast_kernel_for(ef), (size_t)kWarpsPerBlock * (warp_scratch_bytes(cache_log2) + kFastSpillCap * 4)};
   }
+  if (idx.n_total <= SeenCache<true>::max_ids(cache2_log2<true>())) {
+    cache_log2 = cache2_log2<true>();
+    return {count ? v2_kernel_for<true, true>(ef) : v2_kernel_for<true, false>(ef), (size_t)kWarpsPerBlock * warp_scratch2_bytes<true>(cache_log2)};
+  }
+  cache_log2 = cache2_log2<false>();
+  return {count ? v2_kernel_for<false, true>(ef) : v2_kernel_for<false, false>(ef), (size_t)kWarpsPerBlock * warp_scratch2_bytes<false>(cache_log2)};
 }
 
 }  // namespace
@@ -476,8 +631,9 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   }
   if (ef == 0) ef = 1;  // nsw.rs:167-176 behaves identically for ef = 0 and ef = 1
 
-  std::lock_guard<std::mutex> lock(idx.mu);
-  idx.last_search_ms = 0.0;
+  WorkspaceLease lease(idx);  // this call's own control words / tables: concurrent callers do not serialise
+  SearchWorkspace& ws = *lease.ws;
+  double search_ms = 0.0;
   SearchParams p{};
   p.sk = idx.d_sk;
   p.adj = idx.d_adj;
@@ -497,18 +653,6 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   p.flags = flags;
   p.ef_cap = (ef + 31u) / 32u * 32u;
 
-  const size_t smem = (size_t)kWarpsPerBlock * p.ef_cap * 8 + (size_t)kWarpsPerBlock * 32 * 4;
-  HB_CUDA(cudaFuncSetAttribute(hnsw_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int blocks_per_sm = 0;
-  HB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, hnsw_search_kernel, kWarpsPerBlock * 32, smem));
-  HB_REQUIRE(blocks_per_sm >= 1, HB_ERR_UNSUPPORTED, "beam does not fit in shared memory");
-  const uint32_t max_blocks = (uint32_t)(idx.sm_count * blocks_per_sm);
-
-  // visited-table capacity: V grows ~ 50 * ef on M=256 graphs; start at 128 * ef and quadruple on overflow
-  uint32_t vcap_log2 = std::max(12u, ceil_log2((uint64_t)ef * 128u));
-  const uint32_t vcap_max_log2 = std::min(31u, std::max(vcap_log2, ceil_log2(idx.n_total * 2 + 64)));
-  vcap_log2 = std::min(vcap_log2, vcap_max_log2);
-
   uint64_t todo = nq;
   bool retry = false;
   std::vector<uint32_t> h_status, h_map;
@@ -516,36 +660,24 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   // ---- fast path: beam in registers (ef <= 256) ------------------------------------------------
   static const bool force_large = std::getenv("HB_FORCE_LARGE") != nullptr;
   if (ef <= 256 && !force_large) {
-    static const int env_cache = std::getenv("HB_CACHE_LOG2") ? std::atoi(std::getenv("HB_CACHE_LOG2")) : 0;
-    uint32_t cache_log2 = env_cache >= 5 && env_cache <= 13 ? (uint32_t)env_cache : 9u;
-    const FastLaunch fl = fast_kernel_for(ef);
-    const size_t fsmem = (size_t)kWarpsPerBlock * (warp_scratch_bytes(cache_log2) + kFastSpillCap * 4);
-    HB_CUDA(cudaFuncSetAttribute(fl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+    uint32_t cache_log2 = 0;
+    const FastChoice fc = choose_fast(idx, ef, d_counters != nullptr, cache_log2);
+    HB_CUDA(cudaFuncSetAttribute(fc.fl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fc.smem));
     int fbps = 0;
-    HB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fbps, fl.kernel, kWarpsPerBlock * 32, fsmem));
+    HB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fbps, fc.fl.kernel, kWarpsPerBlock * 32, fc.smem));
     HB_REQUIRE(fbps >= 1, HB_ERR_INTERNAL, "fast search kernel does not fit on an SM");
     const uint32_t fblocks = (uint32_t)std::min<uint64_t>((uint64_t)idx.sm_count * fbps, (nq + kWarpsPerBlock - 1) / kWarpsPerBlock);
-    ensure_common(idx, nq);
-    const SearchWorkspace& ws = idx.ws;
+    ensure_common(ws, nq);
     p.ctl = ws.ctl;
     p.qstatus = ws.qstatus;
     p.qmap = nullptr;
     p.nq = (uint32_t)nq;
-    HB_CUDA(cudaMemsetAsync(ws.ctl, 0, 8 * sizeof(uint32_t), stream));
-    HB_CUDA(cudaEventRecord(idx.ev0, stream));
-    fl.kernel<<<fblocks, kWarpsPerBlock * 32, fsmem, stream>>>(p, cache_log2);
-    count_launches();
-    HB_CUDA(cudaGetLastError());
-    HB_CUDA(cudaEventRecord(idx.ev1, stream));
     uint32_t h_ctl[2] = {0, 0};
-    HB_CUDA(cudaMemcpyAsync(h_ctl, ws.ctl, sizeof h_ctl, cudaMemcpyDeviceToHost, stream));
-    HB_CUDA(cudaStreamSynchronize(stream));
-    {
-      float ms = 0.f;
-      HB_CUDA(cudaEventElapsedTime(&ms, idx.ev0, idx.ev1));
-      idx.last_search_ms += ms;
+    search_ms += timed_launch(ws, stream, h_ctl, 2, [&] { fc.fl.kernel<<<fblocks, kWarpsPerBlock * 32, fc.smem, stream>>>(p, cache_log2); });
+    if (!h_ctl[1]) {
+      idx.last_search_ms = search_ms;
+      return;
     }
-    if (!h_ctl[1]) return;
     // boundary-tie stack overflow (tie-heavy data): rerun exactly those queries on the large-capacity kernel
     h_status.resize(nq);
     HB_CUDA(cudaMemcpy(h_status.data(), ws.qstatus, nq * 4, cudaMemcpyDeviceToHost));
@@ -556,12 +688,23 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     retry = true;
   }
 
+  // ---- large-capacity kernel: beam in shared memory, exact visited tables in global memory -----------------------
+  const size_t smem = (size_t)kWarpsPerBlock * p.ef_cap * 8 + (size_t)kWarpsPerBlock * 32 * 4;
+  HB_CUDA(cudaFuncSetAttribute(hnsw_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int blocks_per_sm = 0;
+  HB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, hnsw_search_kernel, kWarpsPerBlock * 32, smem));
+  HB_REQUIRE(blocks_per_sm >= 1, HB_ERR_UNSUPPORTED, "beam does not fit in shared memory");
+  const uint32_t max_blocks = (uint32_t)(idx.sm_count * blocks_per_sm);
+  // visited-table capacity: V grows ~ 50 * ef on M=256 graphs; start at 128 * ef and quadruple on overflow
+  uint32_t vcap_log2 = std::max(12u, ceil_log2((uint64_t)ef * 128u));
+  const uint32_t vcap_max_log2 = std::min(31u, std::max(vcap_log2, ceil_log2(idx.n_total * 2 + 64)));
+  vcap_log2 = std::min(vcap_log2, vcap_max_log2);
+
   for (;;) {
     uint32_t blocks = (uint32_t)std::min<uint64_t>(max_blocks, (todo + kWarpsPerBlock - 1) / kWarpsPerBlock);
     // bound scratch memory for the (rare) big-table retries
     while (blocks > 1 && ((size_t)blocks * kWarpsPerBlock << vcap_log2) * 4 > (size_t)2 << 30) blocks = (blocks + 1) / 2;
-    ensure_workspace(idx, vcap_log2, blocks * kWarpsPerBlock, nq, stream);
-    const SearchWorkspace& ws = idx.ws;
+    ensure_tables(ws, vcap_log2, blocks * kWarpsPerBlock, nq, stream);
     p.vis = ws.vis;
     p.spill = ws.spill;
     p.ctl = ws.ctl;
@@ -570,20 +713,8 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     p.nq = (uint32_t)todo;
     p.vcap_log2 = ws.vcap_log2;
     p.spill_cap = ws.spill_cap;
-    HB_CUDA(cudaMemsetAsync(ws.ctl, 0, 8 * sizeof(uint32_t), stream));
-    HB_CUDA(cudaEventRecord(idx.ev0, stream));
-    hnsw_search_kernel<<<blocks, kWarpsPerBlock * 32, smem, stream>>>(p);
-    count_launches();
-    HB_CUDA(cudaGetLastError());
-    HB_CUDA(cudaEventRecord(idx.ev1, stream));
     uint32_t h_ctl[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    HB_CUDA(cudaMemcpyAsync(h_ctl, ws.ctl, sizeof h_ctl, cudaMemcpyDeviceToHost, stream));
-    HB_CUDA(cudaStreamSynchronize(stream));
-    {
-      float ms = 0.f;
-      HB_CUDA(cudaEventElapsedTime(&ms, idx.ev0, idx.ev1));
-      idx.last_search_ms += ms;
-    }
+    search_ms += timed_launch(ws, stream, h_ctl, 8, [&] { hnsw_search_kernel<<<blocks, kWarpsPerBlock * 32, smem, stream>>>(p); });
 #ifdef HB_DEBUG_BOUNDS
     HB_REQUIRE(h_ctl[2] == 0, HB_ERR_INTERNAL,
                "bounds check " + std::to_string(h_ctl[2]) + " value " + std::to_string(h_ctl[3]) + " query " + std::to_string(h_ctl[4]) +
@@ -607,9 +738,7 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     retry = true;
     vcap_log2 = std::min(vcap_log2 + 2, vcap_max_log2);
   }
-  if (flags & HB_PAD_LIKE_CLI) {
-    // Indexes::search panics on an empty result (main.rs:472); with an entry point every search finds >= 1
-  }
+  idx.last_search_ms = search_ms;
 }
 
 }  // namespace hb

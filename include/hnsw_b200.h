@@ -199,6 +199,57 @@ typedef struct hb_build_params {
 } hb_build_params;
 int hb_build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params* p, int device, int keep_host, hb_index** out);
 
+/* ---- multi-GPU (new: the reference is one process on one host and its only scaling hook is the
+ * `--start/--len` row sub-range of `index` / `ground-truth`, cli/src/main.rs:596-602,698-704,136-140) ---------------
+ * REPLICATE: every device holds the whole index, Index::knns (src/index/mod.rs:28-42) splits the batch contiguously,
+ *            outputs go to disjoint slices in input order; no data-path collective.
+ * SHARD:     device r holds rows [start_r, start_r+len_r) (`-b start_r -l len_r`), searches them for all queries;
+ *            per-shard (distance, key) lists are exchanged with one ncclAllGather and merged exactly. */
+typedef enum hb_multi_mode { HB_MULTI_REPLICATE = 0, HB_MULTI_SHARD = 1 } hb_multi_mode;
+
+/* One rank of an NCCL communicator bound to one device; for hosts that run one process per GPU. */
+typedef struct hb_comm hb_comm;
+#define HB_COMM_ID_BYTES 128
+int hb_comm_unique_id(uint8_t id[HB_COMM_ID_BYTES]); /* rank 0 makes it; the host distributes it to every rank */
+int hb_comm_init_rank(const uint8_t id[HB_COMM_ID_BYTES], int nranks, int rank, int device, hb_comm** out);
+void hb_comm_free(hb_comm* c);
+/* device time (ms) of the phases of the rank's last sharded call: [0] search, [1] all-gather, [2] merge */
+int hb_comm_phase_ms(hb_comm* c, double ms[3]);
+/* collective: `ground-truth` over row shards.  d_shard = this rank's rows (first global key = key_offset), d_queries
+ * = the full batch on every rank; d_packed (nq, k) receives the GLOBAL result on every rank.  Asynchronous on stream. */
+int hb_ground_truth_sharded_device(hb_comm* c, const void* d_shard, uint64_t n_local, uint64_t key_offset, const void* d_queries,
+                                   uint64_t nq, uint32_t k, void* d_packed, void* stream);
+/* collective: sharded HNSW.  idx = the index over this rank's rows (local keys). */
+int hb_knns_sharded_device(hb_comm* c, const hb_index* idx, uint64_t key_offset, const void* d_queries, uint64_t nq, uint32_t k,
+                           uint32_t ef, void* d_packed, void* stream);
+/* collective: replicate rank `root`'s index on every rank GPU-to-GPU (ncclBroadcast of the device arrays).  The root
+ * passes src and gets it back in *out; the others pass NULL and own the replica they receive (no host copy). */
+int hb_index_broadcast(hb_comm* c, hb_index* src, int root, hb_index** out);
+
+/* One process driving N devices (what a Rust/C caller of this ABI uses: ncclCommInitAll + one host thread per device
+ * inside the library). */
+typedef struct hb_multi hb_multi;
+int hb_multi_create(const int* devices, int ndev, hb_multi** out);
+void hb_multi_free(hb_multi* m);
+int hb_multi_device_count(const hb_multi* m);
+uint64_t hb_multi_size(const hb_multi* m); /* Index::size over all devices' rows */
+/* REPLICATE: read_index (main.rs:224-234) once onto devices[0], then broadcast over NVLink */
+int hb_multi_load_idx(hb_multi* m, const char* path);
+/* REPLICATE an index living on devices[0]; `src` stays owned by the caller and must outlive `m` */
+int hb_multi_replicate(hb_multi* m, const hb_index* src);
+/* SHARD: device r builds an HNSW over rows [r*n/N, (r+1)*n/N) of the host array (`index -b -l`), concurrently */
+int hb_multi_build_sharded(hb_multi* m, const uint64_t* data, uint64_t n, const hb_build_params* p);
+/* SHARD from files: paths[r] = shard r's .idx, key_offsets[r] = global key of its first row */
+int hb_multi_load_shards(hb_multi* m, const char* const* paths, const uint64_t* key_offsets);
+/* Index::knns through Indexes::search over all devices; HOST buffers, same contract as hb_knns */
+int hb_multi_knns(hb_multi* m, const uint64_t* queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, uint64_t* keys,
+                  uint64_t* dists, uint32_t* found);
+/* `ground-truth` with the rows sharded over the devices; HOST buffers, same contract as hb_ground_truth */
+int hb_multi_ground_truth(hb_multi* m, const uint64_t* data, uint64_t n, const uint64_t* queries, uint64_t nq, uint32_t k,
+                          uint64_t* keys, uint64_t* dists);
+int hb_multi_phase_ms(hb_multi* m, double ms[3]);
+const hb_index* hb_multi_index(const hb_multi* m, int r); /* device r's replica / shard, borrowed */
+
 #ifdef __cplusplus
 }
 #endif
