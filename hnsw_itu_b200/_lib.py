@@ -44,7 +44,7 @@ class SynthParamsC(C.Structure):
 
 class BuildParamsC(C.Structure):
     _fields_ = [("ef_construction", C.c_uint32), ("connections", C.c_uint32), ("max_connections", C.c_uint32),
-                ("rayon_threads", C.c_uint32), ("serial_prefix", C.c_uint32)]
+                ("rayon_threads", C.c_uint32), ("serial_prefix", C.c_uint32), ("nsw", C.c_uint32)]
 
 
 def build_library(force: bool = False) -> str:
@@ -68,6 +68,18 @@ def lib() -> C.CDLL:
         raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                           "(hnsw_itu_b200 has no CPU fallback)")
     L = C.CDLL(LIB_PATH)
+    if os.environ.get("HB_LIB_PATH"):
+        # an A/B build (tools/ab.py) may predate the newest entry points: binding a missing symbol is skipped, calling it fails
+        class _Tolerant:
+            def __init__(self, lib):
+                object.__setattr__(self, "_lib", lib)
+
+            def __getattr__(self, name):
+                try:
+                    return getattr(self._lib, name)
+                except AttributeError:
+                    return C.CFUNCTYPE(C.c_int)(lambda: HB_ERR_UNSUPPORTED)
+        L = _Tolerant(L)
     vp = C.c_void_p
     L.hb_last_error.restype = C.c_char_p
     L.hb_version.restype = C.c_int
@@ -79,6 +91,7 @@ def lib() -> C.CDLL:
     L.hb_index_set_attrs.argtypes = [vp, C.c_double, C.c_char_p]
     L.hb_index_get_attrs.argtypes = [vp, C.POINTER(C.c_int), _u64p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_char_p,
                                      C.c_uint64, C.c_char_p, C.c_uint64]
+    L.hb_index_set_format_size.argtypes = [vp, C.c_int]
     L.hb_index_free.argtypes = [vp]
     L.hb_index_free.restype = None
     L.hb_index_size.argtypes = [vp]
@@ -101,6 +114,7 @@ def lib() -> C.CDLL:
     L.hb_pack_device.argtypes = [vp, vp, vp, C.c_uint64, C.c_uint32, C.c_uint64, vp, vp]
     L.hb_synth_device.argtypes = [C.POINTER(SynthParamsC), C.c_uint64, C.c_uint64, vp, vp]
     L.hb_build_hnsw.argtypes = [_u64p, C.c_uint64, C.POINTER(BuildParamsC), C.c_int, C.c_int, C.POINTER(vp)]
+    L.hb_tensor_peak.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double)]
     # multi-GPU (multi.cu)
     u8p, dbl3 = C.POINTER(C.c_uint8), C.POINTER(C.c_double)
     L.hb_comm_unique_id.argtypes = [u8p]

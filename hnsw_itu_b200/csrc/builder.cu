@@ -480,7 +480,7 @@ Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& bp, i
   if (n == 0) {
     std::vector<HostGraph> g(1);
     g[0].off.assign(1, 0);
-    return index_from_host(HB_ALGO_HNSW, std::move(g), -1, device, keep_host);
+    return index_from_host(bp.nsw ? HB_ALGO_NSW : HB_ALGO_HNSW, std::move(g), -1, device, keep_host);
   }
 
   // ---- plan: steps, levels, layer sizes (all host-side and deterministic) -----------------------------------
@@ -490,8 +490,11 @@ Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& bp, i
   std::vector<Step> steps;
   steps.reserve(prefix + (n - prefix) / chunk + 2);
   steps.push_back(Step{0, 1, 0, true});  // first point: level = layers.len() = 0 (hnsw.rs:185-190)
-  for (uint64_t i = 1; i < prefix; ++i) steps.push_back(Step{i, 1, rng.level(m), true});
-  for (uint64_t i = prefix; i < n; i += chunk) steps.push_back(Step{i, (uint32_t)std::min<uint64_t>(chunk, n - i), rng.level(m), false});
+  // NSWBuilder (nsw.rs:224-322) is the same insertion with every point on the base graph only and ep = the first point
+  const bool nsw = bp.nsw != 0;
+  for (uint64_t i = 1; i < prefix; ++i) steps.push_back(Step{i, 1, nsw ? 0u : rng.level(m), true});
+  for (uint64_t i = prefix; i < n; i += chunk)
+    steps.push_back(Step{i, (uint32_t)std::min<uint64_t>(chunk, n - i), nsw ? 0u : rng.level(m), false});
   uint32_t n_layers = 0;
   for (const Step& s : steps) n_layers = std::max(n_layers, s.level);
   const size_t G = (size_t)n_layers + 1;
@@ -519,7 +522,7 @@ Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& bp, i
   // ---- device arrays ------------------------------------------------------------------------------------
   std::unique_ptr<Index> idx(new Index());
   idx->device = device;
-  idx->algo = HB_ALGO_HNSW;
+  idx->algo = nsw ? HB_ALGO_NSW : HB_ALGO_HNSW;
   idx->n_total = n_total;
   idx->n_base = n;
   idx->stride = (M + 1 + 64 + 31) / 32 * 32;  // M + 1 after pruning (nsw.rs:129) plus room for one step's appends
@@ -641,7 +644,7 @@ Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& bp, i
   idx->attrs.format_size = true;
   idx->attrs.data = "hamming";
   idx->attrs.size = n;
-  idx->attrs.algo = HB_ALGO_HNSW;
+  idx->attrs.algo = nsw ? HB_ALGO_NSW : HB_ALGO_HNSW;
   idx->attrs.params = "index=(efc=" + std::to_string(efc) + ",m=" + std::to_string(m) + ",M=" + std::to_string(M) + ")";  // main.rs:171-174
   if (keep_host) {
     export_graphs(*idx, data, up_point, idx->host);

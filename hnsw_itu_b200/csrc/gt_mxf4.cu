@@ -20,6 +20,7 @@
 #include <algorithm>
 #include <climits>
 
+#include "gt_common.cuh"
 #include "hb_internal.h"
 
 #ifndef HB_GT_PROBE_MMAS
@@ -32,7 +33,6 @@
 namespace hb {
 namespace {
 
-constexpr uint64_t kNone = ~0ull;
 constexpr int kTileM = 128;   // queries per work item (UMMA M)
 constexpr int kTileN = 240;   // data rows per accumulator tile (UMMA N): 2 x 240 + 16 scale-factor columns <= 512
 constexpr int kGroup = 48;      // accumulator columns an epilogue thread reads per step (240 = 5 x 48)
@@ -58,73 +58,8 @@ constexpr uint32_t kSmemBytes = kBarOffset + 192 + 1024;  // + barriers + alignm
 // scale format E8M0, scale-factor ids 0, N = 240, M = 128, K = 64
 constexpr uint32_t kIdesc = (1u << 7) | (1u << 10) | (1u << 23) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-// Bounded spin: a protocol bug traps (the launch fails with an error) instead of hanging the GPU.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t done = 0;
-  long long t0 = 0;
-  for (uint32_t spins = 0; !done; ++spins) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(bar), "r"(parity), "r"(HB_GT_SUSPEND_NS)  // suspend-time hint: the warp sleeps in the barrier unit instead of spinning
-        : "memory");
-    if (!done && (spins & 15u) == 15u) {
-      const long long now = clock64();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > 6000000000ll) __trap();  // ~3 s: no wait in this kernel is longer than a few ms
-    }
-  }
-}
-
-// K-major, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart (cute::UMMA::SmemDescriptor layout, version 1)
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
-
-__device__ __forceinline__ void umma_mxf4(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t tmem_sf, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%5], p;\n\t}" ::"r"(tmem_d),
-      "l"(da), "l"(db), "r"(kIdesc), "r"(accumulate), "r"(tmem_sf)
-      : "memory");
-}
-// one lane of the (converged) warp; ptxas knows the guarded region is single-threaded, so UTCIMMA needs no lane loop
-__device__ __forceinline__ uint32_t elect_one_sync() {
-  uint32_t pred = 0;
-  asm volatile(
-      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
-      "elect.sync rx|px, %1;\n\t"
-      "@px mov.s32 %0, 1;\n\t}"
-      : "+r"(pred)
-      : "r"(0xFFFFFFFFu));
-  return pred;
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-
-#define HB_TMEM_LD32(v, taddr)                                                                                          \
-  asm volatile(                                                                                                         \
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                         \
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "                                         \
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"                         \
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),     \
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),          \
-        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),         \
-        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                       \
-      : "r"(taddr)                                                                                                      \
-      : "memory")
+using namespace gt;  // mbarrier / tcgen05 helpers, HB_TMEM_LD32 (gt_common.cuh)
+constexpr auto mbar_wait = gt::mbar_wait<HB_GT_SUSPEND_NS>;
 
 #ifdef HB_GT_DIAG
 // per-CTA phase clocks (diagnostic build only, tools/gt_diag.py): [0] kernel cycles, [1] MMA warp waiting for a free
@@ -703,7 +638,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
             const uint64_t da = da0 + (uint64_t)(kb * (kAKBlockBytes >> 4)), db = db0 + (uint64_t)(stage * (kStageBytes >> 4));
 #pragma unroll
             for (int j = 0; j < HB_GT_PROBE_MMAS; ++j)  // K = 64 E2M1 per instruction: +32 B inside the swizzle atom = +2 in the encoded address
-              umma_mxf4(tmem_d, da + 2 * j, db + 2 * j, tmem + kSfCol, (kb | j) != 0);
+              umma_mxf4(tmem_d, da + 2 * j, db + 2 * j, kIdesc, tmem + kSfCol, (kb | j) != 0);
             umma_commit(bEmpty + 8 * stage);
             if (kb == kKBlocks - 1) {
               umma_commit(bTFull + 8 * acc);

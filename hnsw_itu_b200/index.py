@@ -211,10 +211,11 @@ def ground_truth(data, queries, k: int, device: int = 0, algo: str = "auto"):
 
 
 def build_hnsw(data, efc: int = 96, m: int = 24, M: int = 256, rayon_threads: int = 16, device: int = 0, keep_host: bool = True,
-               serial_prefix: int = 0) -> Index:
-    """HNSWBuilder::extend_parallel (src/index/hnsw.rs:44-169) with the searches on the device."""
+               serial_prefix: int = 0, nsw: bool = False) -> Index:
+    """HNSWBuilder::extend_parallel (src/index/hnsw.rs:44-169) with the searches on the device; nsw=True builds the
+    single-graph NSW variant instead (NSWBuilder::extend_parallel, src/index/nsw.rs:224-322)."""
     d = _sketches(data)
-    bp = BuildParamsC(efc, m, M, rayon_threads, serial_prefix)
+    bp = BuildParamsC(efc, m, M, rayon_threads, serial_prefix, int(nsw))
     h = C.c_void_p()
     check(_lib.lib().hb_build_hnsw(_p(d), len(d), C.byref(bp), device, int(keep_host), C.byref(h)))
     return Index(h.value)

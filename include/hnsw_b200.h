@@ -107,6 +107,8 @@ int hb_index_from_parts(int algo, uint32_t n_graphs, const uint64_t* n_nodes, co
 int hb_index_save_idx(const hb_index* idx, const char* path);
 /* ResultAttrs carried by the .idx (main.rs:311-320); params is "index=(efc=..,m=..,M=..)" */
 int hb_index_set_attrs(hb_index* idx, double buildtime, const char* params);
+/* ResultAttrs.format_size: false when the index covers a `--start/--len` sub-range (main.rs:122) */
+int hb_index_set_format_size(hb_index* idx, int format_size);
 /* ResultAttrs as loaded / set (main.rs:311-320): what write_result copies into the result file (main.rs:287-306).
  * data/params are copied into caller buffers (NUL-terminated, truncated to cap); any pointer may be NULL. */
 int hb_index_get_attrs(const hb_index* idx, int* format_size, uint64_t* size, double* buildtime, double* querytime,
@@ -169,6 +171,12 @@ int hb_ground_truth_algo(const uint64_t* data, uint64_t n, const uint64_t* queri
 int hb_ground_truth_device_algo(const void* d_data, uint64_t n, uint64_t key_offset, const void* d_queries, uint64_t nq,
                                 uint32_t k, int algo, void* d_packed, void* stream);
 
+/* Measured peak of the tensor pipe for the instruction the ground-truth kernels issue (same tile shape and shared-memory
+ * layout, nothing else in the kernel): kind 0 = tcgen05.mma kind::mxf4.block_scale (E2M1, M128 N240 K64), 1 = kind::i8
+ * (M128 N256 K32).  *tops = 10^12 operations/s (2*M*N*K per instruction) over all SMs.  The roofline denominator of
+ * the `ground-truth` path (new: MEASURED_PEAKS.json only carries a bf16 cuBLAS figure). */
+int hb_tensor_peak(int device, int kind, double* tops);
+
 /* Exact (distance, key) merge of n_lists per-shard lists laid out
  * (n_lists, nq, k) packed u64 -> (nq, k) packed (new for sharding; the order
  * is total so the merge equals a global Bruteforce + sort). */
@@ -196,6 +204,7 @@ typedef struct hb_build_params {
   uint32_t max_connections; /* -M, default 256 */
   uint32_t rayon_threads;   /* stands in for rayon::current_num_threads(): chunk = 32 * this, and it is mixed into the level seed */
   uint32_t serial_prefix;   /* points inserted one at a time before chunking starts; 0 = the reference's 50 000 (hnsw.rs:54) */
+  uint32_t nsw;             /* != 0: NSWBuilder::extend_parallel (src/index/nsw.rs:224-322): one graph, no upper layers; the handle is an NSW index */
 } hb_build_params;
 int hb_build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params* p, int device, int keep_host, hb_index** out);
 
