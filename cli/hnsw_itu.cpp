@@ -324,7 +324,9 @@ void query_and_write(const Args& a, hb_index* idx) {
   at.algo = algo_name(info.algo);
   at.querytime = secs;
   at.params = std::string(params) + ",query=(ef=" + std::to_string(ef) + ")";  // main.rs:218-219
-  write_results(a.str("outfile", "result.h5"), nq, k, std::move(keys), nullptr, at);
+  // the reference writes only `knns` (main.rs:261-309); the raw side-file form also keeps the distances
+  const std::string out = a.str("outfile", "result.h5");
+  write_results(out, nq, k, std::move(keys), is_h5_name(out) ? nullptr : &dists, at);
   if (multi) hb_multi_free(multi);
 }
 

@@ -92,6 +92,7 @@ def lib() -> C.CDLL:
     L.hb_index_get_attrs.argtypes = [vp, C.POINTER(C.c_int), _u64p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_char_p,
                                      C.c_uint64, C.c_char_p, C.c_uint64]
     L.hb_index_set_format_size.argtypes = [vp, C.c_int]
+    L.hb_index_compact.argtypes = [vp]
     L.hb_index_free.argtypes = [vp]
     L.hb_index_free.restype = None
     L.hb_index_size.argtypes = [vp]

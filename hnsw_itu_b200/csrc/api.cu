@@ -229,6 +229,10 @@ int hb_index_set_attrs(hb_index* h, double buildtime, const char* params) {
   });
 }
 
+int hb_index_compact(hb_index* h) {
+  return guarded([&] { index_compact(*as_index(h)); });
+}
+
 int hb_index_set_format_size(hb_index* h, int format_size) {
   return guarded([&] { as_index(h)->attrs.format_size = format_size != 0; });
 }
@@ -244,7 +248,7 @@ int hb_index_get_info(const hb_index* h, hb_index_info* info) {
     info->algo = idx->algo;
     info->device = idx->device;
     info->n_graphs = idx->algo == HB_ALGO_BRUTEFORCE ? 0u : (uint32_t)idx->g_nodes.size();
-    info->row_stride = idx->stride;
+    info->row_stride = idx->d_rowoff ? 0 : idx->stride;
     info->size = idx->n_base;
     info->n_nodes_total = idx->n_total;
     uint64_t e = 0;

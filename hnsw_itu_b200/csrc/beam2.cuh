@@ -92,15 +92,15 @@ __device__ __forceinline__ uint32_t hamming_rows(const uint4* __restrict__ sk, c
   return __shfl_sync(kFullMask, z, ((lane & 7u) << 2) | (lane >> 3));  // row i sits in lane 4 (i % 8) + i / 8
 }
 
-// How the neighbour sketches travel: 0 = LDG into registers (hamming_rows above); 1 = cp.async into a per-warp stage of
-// 32 rows, the next group of 32 issued before the accept replay of the current one; 2 = a stage of 64 rows, both groups
-// of a segment issued together (one DRAM round trip per expansion).  Measured on B200: a dependent 32-row gather by
-// one warp costs ~2 050 cycles through cp.async against ~2 900 through LDG.128 (profiles/r01c_gather_shape_microbench.log),
-// and cp.async holds no registers while the rows are in flight.
+// How the neighbour sketches travel: 1 (default) = cp.async into a per-warp stage of 32 rows, the next group of 32 issued
+// before the accept replay of the current one; 0 = LDG into registers (hamming_rows above).  Measured on B200: a
+// dependent 32-row gather by one warp costs ~2 050 cycles through cp.async against ~2 900 through LDG.128
+// (profiles/r01c_gather_shape_microbench.log), and cp.async holds no registers while the rows are in flight, which is
+// worth one more resident CTA per SM: 8.5-8.7 against 8.3 M queries/s (profiles/r02d_ab_gather_variants.log).
 #ifndef HB_GATHER2
-#define HB_GATHER2 0
+#define HB_GATHER2 1
 #endif
-constexpr uint32_t kStageRows2 = HB_GATHER2 == 2 ? 64u : (HB_GATHER2 == 1 ? 32u : 0u);
+constexpr uint32_t kStageRows2 = HB_GATHER2 == 1 ? 32u : 0u;
 constexpr uint32_t kStageBytes2 = kStageRows2 * 128u;
 
 // stage slot of (pass p, half h) for this lane: lane-private 16-B slots, consecutive lanes in consecutive slots
@@ -117,11 +117,10 @@ __device__ __forceinline__ void gather_issue(const uint4* __restrict__ sk, const
     }
   asm volatile("cp.async.commit_group;" ::: "memory");
 }
-template <int PENDING>
 __device__ __forceinline__ uint32_t gather_finish(uint32_t n, const QueryRegs& q, const uint4* stage) {
   const uint32_t lane = threadIdx.x & 31, c = lane & 3u;
   const uint4* const mine = stage + lane;
-  asm volatile("cp.async.wait_group %0;" ::"n"(PENDING) : "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   uint32_t x[4];
 #pragma unroll
   for (int p = 0; p < 4; ++p) x[p] = (8u * p < n) ? popc_xor4(mine[(2 * p) * 32], q.a) + popc_xor4(mine[(2 * p + 1) * 32], q.b) : 0u;
@@ -252,6 +251,20 @@ struct BeamSplit {
     return true;
   }
 
+  // the key pop_unexpanded() would return next if nothing were inserted in between (kNoKey: none); nothing is marked
+  __device__ __forceinline__ uint32_t peek_unexpanded() const {
+    uint32_t cd = kEmpty32;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+      if (!(wd[r] & 1u)) cd = min(cd, wd[r]);
+    const uint32_t md = __reduce_min_sync(kFullMask, cd);
+    uint32_t ck = kEmpty32;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+      if (wd[r] == md) ck = min(ck, wk[r]);
+    return md == kEmpty32 ? kNoKey : __reduce_min_sync(kFullMask, ck);
+  }
+
   // w.push((d, key)) while |w| < ef (nsw.rs:171-172)
   __device__ __forceinline__ void push(uint32_t d, uint32_t key, uint32_t ef) {
     const uint32_t lane = threadIdx.x & 31;
@@ -350,15 +363,6 @@ __host__ __device__ constexpr size_t warp_scratch2_bytes(uint32_t entries_log2) 
   return SeenCache<TAG16>::bytes(entries_log2) + (size_t)(kIdsWords2 + kSpillCap2) * 4 + kStageBytes2;
 }
 
-// 1 = L2-prefetch the sketch rows of the second group of 32 of a segment while the first group is processed
-#ifndef HB_PF_GROUP2
-#define HB_PF_GROUP2 0
-#endif
-// 1 = L2-prefetch the adjacency row of every accepted candidate (it is expanded later with high probability)
-#ifndef HB_PF_ACCEPT
-#define HB_PF_ACCEPT 0
-#endif
-
 // nsw::search(graph, q, ef, ep) (nsw.rs:133-184) on the graph that contains gid `ep`.  On return b holds w.
 // status != 0: the boundary-tie stack overflowed (the caller reruns the query on the large-capacity kernel).
 // COUNT = false drops the X/E/V/A work counters (four registers and their updates) from the timed path.
@@ -389,8 +393,10 @@ __device__ __forceinline__ void beam_search2(const GraphView& gv, const QueryReg
     }
     if (COUNT) ++c.X;
     // ---- for e in graph.neighborhood(c.key)  (nsw.rs:156) ----
-    const uint32_t* row = gv.adj + (size_t)ckey * gv.stride;
-    uint32_t w0 = __ldg(row + lane), w1 = __ldg(row + 32 + lane);
+    const uint32_t* row = gv.row(ckey);
+    uint32_t w0, w1;
+    w0 = __ldg(row + lane);
+    w1 = __ldg(row + 32 + lane);
     const uint32_t deg = __shfl_sync(kFullMask, w0, 0);
     if (COUNT) c.E += deg;
     for (uint32_t base = 0; base <= deg; base += 64) {
@@ -415,30 +421,16 @@ __device__ __forceinline__ void beam_search2(const GraphView& gv, const QueryReg
       if (lane < kIdsPad) ws.ids[n_new + lane] = ckey;  // padding rows: any valid gid
       if (COUNT) c.V += n_new;
       __syncwarp();
-#if HB_PF_GROUP2
-      // more than one group of 32: pull the second group's sketch rows into L2 while the first group is gathered
-      // and replayed, so that its gather is not a second full DRAM round trip
-      if (32u + lane < n_new) {
-        const char* r2 = reinterpret_cast<const char*>(gv.sk + (size_t)ws.ids[32u + lane] * 8);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) prefetch_l2(r2 + 32 * i);
-      }
-#endif
 #if HB_GATHER2 == 1
       if (n_new) gather_issue(gv.sk, ws.ids, min(32u, n_new), ws.stage);
-#elif HB_GATHER2 == 2
-      if (n_new) gather_issue(gv.sk, ws.ids, min(32u, n_new), ws.stage);
-      if (n_new > 32u) gather_issue(gv.sk, ws.ids + 32, n_new - 32u, ws.stage + 256);
 #endif
       for (uint32_t g0 = 0; g0 < n_new; g0 += 32) {
         const uint32_t n = min(32u, n_new - g0);
         const uint32_t myid = ws.ids[g0 + lane];
         // distance_fn(point, query) for the group (nsw.rs:164-165)
 #if HB_GATHER2 == 1
-        const uint32_t myd = gather_finish<0>(n, q, ws.stage);
+        const uint32_t myd = gather_finish(n, q, ws.stage);
         if (g0 + 32u < n_new) gather_issue(gv.sk, ws.ids + g0 + 32, n_new - g0 - 32u, ws.stage);  // in flight during the replay
-#elif HB_GATHER2 == 2
-        const uint32_t myd = (g0 == 0 && n_new > 32u) ? gather_finish<1>(n, q, ws.stage) : gather_finish<0>(n, q, ws.stage + (g0 ? 256 : 0));
 #else
         const uint32_t myd = hamming_rows(gv.sk, ws.ids + g0, n, q);
 #endif
@@ -451,9 +443,6 @@ __device__ __forceinline__ void beam_search2(const GraphView& gv, const QueryReg
           const uint32_t nd = __shfl_sync(kFullMask, myd, first), nk = __shfl_sync(kFullMask, myid, first);
           if (b.contains(nk)) continue;  // a revisit the cache no longer remembered
           if (COUNT) ++c.A;
-#if HB_PF_ACCEPT
-          if (lane < 2) prefetch_l2(gv.adj + (size_t)nk * gv.stride + lane * 32);
-#endif
           if (b.size < ef) {
             b.push(nd, nk, ef);
             if (pm && b.size >= ef) pm &= __ballot_sync(kFullMask, myd < b.F());  // the beam just filled: F now binds

@@ -25,6 +25,7 @@
 // directly and hb_index_save_idx writes it in the reference's format.
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cmath>
 #include <cstring>
 #include <memory>
@@ -533,6 +534,7 @@ Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& bp, i
   HB_CUDA(cudaMalloc(&idx->d_adj, n_total * idx->stride * 4ull));
   HB_CUDA(cudaMalloc(&idx->d_down, std::max<uint64_t>(n_upper, 1) * 4));
   idx->device_bytes = n_total * 128 + n_total * idx->stride * 4ull + n_upper * 4;
+  idx->adj_words = n_total * idx->stride;
   HB_CUDA(cudaMemset(idx->d_adj, 0, n_total * idx->stride * 4ull));
   HB_CUDA(cudaMemcpy(idx->d_sk, data, n * 128, cudaMemcpyHostToDevice));
   if (n_upper) {
@@ -651,6 +653,7 @@ Index* build_hnsw(const uint64_t* data, uint64_t n, const hb_build_params& bp, i
     idx->has_host = true;
   }
   idx->attrs.buildtime = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  if (std::getenv("HB_INDEX_LAYOUT") && std::string(std::getenv("HB_INDEX_LAYOUT")) == "compact") index_compact(*idx);
   return idx.release();
 }
 

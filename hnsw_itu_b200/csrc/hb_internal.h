@@ -119,6 +119,9 @@ struct Index {
   uint32_t stride = 0;        // words per adjacency row, multiple of 32 (row = one or more 128-B lines)
   uint4* d_sk = nullptr;      // n_total rows of 128 B
   uint32_t* d_adj = nullptr;  // n_total * stride; word 0 = degree, then global neighbour ids
+  // compact layout (index_compact): row gid starts at line d_rowoff[gid] (128-B lines) and spans ceil((deg + 1) / 32) lines
+  uint32_t* d_rowoff = nullptr;
+  uint64_t adj_words = 0;     // 32-bit words allocated in d_adj
   uint32_t* d_down = nullptr; // n_total - n_base: global id of the same point one graph below
   uint32_t ep_gid = 0;
   uint64_t device_bytes = 0;
@@ -138,6 +141,7 @@ void write_idx_file(const char* path, const Attrs& attrs, int algo, const std::v
 // index.cu
 Index* index_from_host(int algo, std::vector<HostGraph>&& graphs, int64_t ep, int device, bool keep_host);
 void ensure_device(int device);
+void index_compact(Index& idx);  // fixed-stride rows -> line-granular rows + offsets (5x less HBM at M = 256)
 
 // search.cu
 void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, void* d_keys,

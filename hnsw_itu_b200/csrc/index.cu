@@ -19,6 +19,7 @@
 //     (max degree M+1 = 257, nsw.rs:121-129) that is 1152 B/node = 11.5 GB for
 //     10 M nodes out of 180 GB.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 
@@ -45,6 +46,23 @@ __global__ void csr_to_rows_kernel(const uint64_t* __restrict__ off, const uint3
 __global__ void down_to_gid_kernel(const uint64_t* __restrict__ down, uint64_t n, uint32_t below_base, uint32_t* __restrict__ out) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = (uint32_t)down[i] + below_base;
+}
+
+// lines (of 32 words) a row needs: its degree word + deg neighbour ids
+__global__ void row_lines_kernel(const uint32_t* __restrict__ rows, uint32_t stride, uint64_t n, uint32_t* __restrict__ lines) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) lines[i] = (rows[i * stride] + 1u + 31u) / 32u;
+}
+// one warp per node: copy the used lines of its fixed-stride row to its place in the compact array
+__global__ void compact_rows_kernel(const uint32_t* __restrict__ rows, uint32_t stride, uint64_t n, const uint32_t* __restrict__ rowoff,
+                                    uint32_t* __restrict__ out) {
+  const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t lane = threadIdx.x & 31;
+  if (warp >= n) return;
+  const uint32_t* src = rows + warp * stride;
+  const uint32_t words = (rowoff[warp + 1] - rowoff[warp]) * 32u;
+  uint32_t* dst = out + (size_t)rowoff[warp] * 32;
+  for (uint32_t j = lane; j < words; j += 32) dst[j] = src[j];
 }
 
 template <class T>
@@ -87,6 +105,7 @@ Index::~Index() {
   cudaSetDevice(device);
   cudaFree(d_sk);
   cudaFree(d_adj);
+  cudaFree(d_rowoff);
   cudaFree(d_down);
   ws_pool.clear();
   for (CallBuffers& b : pool) {
@@ -169,6 +188,7 @@ Index* index_from_host(int algo, std::vector<HostGraph>&& graphs, int64_t ep, in
     const uint64_t adj_bytes = total * idx->stride * 4ull;
     HB_CUDA(cudaMalloc(&idx->d_adj, std::max<uint64_t>(adj_bytes, 4)));
     idx->device_bytes += adj_bytes;
+    idx->adj_words = total * idx->stride;
     const uint64_t n_upper = total - idx->n_base;
     HB_CUDA(cudaMalloc(&idx->d_down, std::max<uint64_t>(n_upper, 1) * 4));
     idx->device_bytes += n_upper * 4;
@@ -200,7 +220,51 @@ Index* index_from_host(int algo, std::vector<HostGraph>&& graphs, int64_t ep, in
     idx->host = std::move(graphs);
     idx->has_host = true;
   }
+  static const bool compact = std::getenv("HB_INDEX_LAYOUT") && std::string(std::getenv("HB_INDEX_LAYOUT")) == "compact";
+  if (compact) index_compact(*idx);
   return idx.release();
+}
+
+// Fixed-stride rows cost address space, not bandwidth -- but at M = 256 that is 1 408 B per node (16 GB for 10 M points)
+// for ~190 B of ids.  The compact layout keeps each row's used 128-B lines back to back and finds a row through one
+// 32-bit line offset per node: ~3 GB for the same index, at the price of one more dependent 4-byte read per expansion.
+void index_compact(Index& idx) {
+  if (idx.d_rowoff || idx.algo == HB_ALGO_BRUTEFORCE || idx.n_total == 0) return;
+  HB_CUDA(cudaSetDevice(idx.device));
+  const uint64_t n = idx.n_total;
+  DevBuf<uint32_t> d_lines(n);
+  row_lines_kernel<<<(unsigned)((n + 255) / 256), 256>>>(idx.d_adj, idx.stride, n, d_lines.p);
+  count_launches();
+  HB_CUDA(cudaGetLastError());
+  std::vector<uint32_t> lines(n), off(n + 1);
+  HB_CUDA(cudaMemcpy(lines.data(), d_lines.p, n * 4, cudaMemcpyDeviceToHost));
+  uint64_t total = 0;
+  for (uint64_t i = 0; i < n; ++i) {
+    off[i] = (uint32_t)total;
+    total += lines[i];
+  }
+  HB_REQUIRE(total < 0xFFFFFFFFull, HB_ERR_UNSUPPORTED, "compact adjacency above 2^32 lines");
+  off[n] = (uint32_t)total;
+  uint32_t *d_off = nullptr, *d_out = nullptr;
+  HB_CUDA(cudaMalloc(&d_off, (n + 1) * 4));
+  const uint64_t words = (total + 1) * 32;  // + one line: the search always loads two lines of a row
+  cudaError_t e = cudaMalloc(&d_out, words * 4);
+  if (e != cudaSuccess) {
+    cudaFree(d_off);
+    HB_CUDA(e);
+  }
+  HB_CUDA(cudaMemcpy(d_off, off.data(), (n + 1) * 4, cudaMemcpyHostToDevice));
+  HB_CUDA(cudaMemset(d_out + total * 32, 0, 128));
+  compact_rows_kernel<<<(unsigned)((n * 32 + 255) / 256), 256>>>(idx.d_adj, idx.stride, n, d_off, d_out);
+  count_launches();
+  HB_CUDA(cudaGetLastError());
+  HB_CUDA(cudaDeviceSynchronize());
+  idx.device_bytes -= idx.adj_words * 4;
+  cudaFree(idx.d_adj);
+  idx.d_adj = d_out;
+  idx.d_rowoff = d_off;
+  idx.adj_words = words;
+  idx.device_bytes += words * 4 + (n + 1) * 4;
 }
 
 }  // namespace hb

@@ -197,7 +197,7 @@ void knns_sharded(Comm& c, const Index& idx, uint64_t key_offset, const void* d_
 // Replicate the index of rank `root` on every rank: metadata first (one small ncclBroadcast of a POD header), then
 // the device arrays GPU-to-GPU.  Returns this rank's index (root gets `src` back).
 struct ReplicaHeader {
-  uint64_t n_total, n_base, device_bytes, n_graphs;
+  uint64_t n_total, n_base, device_bytes, n_graphs, adj_words, compact;
   int64_t ep_file;
   uint32_t stride, ep_gid;
   int32_t algo;
@@ -215,6 +215,7 @@ Index* index_broadcast(Comm& c, Index* src, int root, cudaStream_t s) {
     HB_REQUIRE(src->device == c.device, HB_ERR_INVALID, "index and communicator rank live on different devices");
     HB_REQUIRE(src->g_nodes.size() <= 64, HB_ERR_UNSUPPORTED, "more than 64 graphs");
     h.n_total = src->n_total; h.n_base = src->n_base; h.device_bytes = src->device_bytes; h.n_graphs = src->g_nodes.size();
+    h.adj_words = src->adj_words; h.compact = src->d_rowoff != nullptr;
     h.ep_file = src->ep_file; h.stride = src->stride; h.ep_gid = src->ep_gid; h.algo = src->algo;
     for (size_t g = 0; g < src->g_nodes.size(); ++g) {
       h.g_nodes[g] = src->g_nodes[g]; h.g_edges[g] = src->g_edges[g]; h.g_base[g] = src->g_base[g];
@@ -248,7 +249,9 @@ Index* index_broadcast(Comm& c, Index* src, int root, cudaStream_t s) {
     idx->sm_count = prop.multiProcessorCount;
     HB_CUDA(cudaMalloc(&idx->d_sk, std::max<uint64_t>(h.n_total, 1) * 128));
     if (h.algo != HB_ALGO_BRUTEFORCE) {
-      HB_CUDA(cudaMalloc(&idx->d_adj, std::max<uint64_t>(h.n_total * h.stride * 4ull, 4)));
+      idx->adj_words = h.adj_words;
+      HB_CUDA(cudaMalloc(&idx->d_adj, std::max<uint64_t>(h.adj_words * 4ull, 4)));
+      if (h.compact) HB_CUDA(cudaMalloc(&idx->d_rowoff, (h.n_total + 1) * 4));
       HB_CUDA(cudaMalloc(&idx->d_down, std::max<uint64_t>(h.n_total - h.n_base, 1) * 4));
     }
   }
@@ -262,7 +265,8 @@ Index* index_broadcast(Comm& c, Index* src, int root, cudaStream_t s) {
   };
   bcast(idx->d_sk, h.n_total * 128);
   if (h.algo != HB_ALGO_BRUTEFORCE) {
-    bcast(idx->d_adj, h.n_total * h.stride * 4ull);
+    bcast(idx->d_adj, h.adj_words * 4ull);
+    if (h.compact) bcast(idx->d_rowoff, (h.n_total + 1) * 4);
     bcast(idx->d_down, (h.n_total - h.n_base) * 4);
   }
   HB_CUDA(cudaStreamSynchronize(s));

@@ -42,7 +42,10 @@ namespace {
 
 constexpr uint32_t kFull = 0xFFFFFFFFu;
 constexpr uint32_t kEmpty = 0xFFFFFFFFu;
-constexpr int kWarpsPerBlock = 4;
+#ifndef HB_WARPS
+#define HB_WARPS 4
+#endif
+constexpr int kWarpsPerBlock = HB_WARPS;
 
 #ifdef HB_DEBUG_BOUNDS
 #define HB_CHK(cond, code, val)                                   \
@@ -62,6 +65,7 @@ constexpr int kWarpsPerBlock = 4;
 struct SearchParams {
   const uint4* sk;
   const uint32_t* adj;
+  const uint32_t* rowoff;  // compact layout (nullptr: fixed stride)
   const uint32_t* down;
   const uint4* queries;
   const uint32_t* qmap;  // optional indirection for retries
@@ -228,13 +232,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) hnsw_search_kernel(con
         ++X;
         // ---- for e in graph.neighborhood(c.key)  (nsw.rs:156) ------------------
         HB_CHK(ckey < p.n_total, 2, ckey);
-        const uint32_t* row = p.adj + (size_t)ckey * p.stride;
+        const uint32_t* row = p.rowoff ? p.adj + (size_t)__ldg(p.rowoff + ckey) * 32 : p.adj + (size_t)ckey * p.stride;
         uint32_t word = __ldg(row + lane);
         const uint32_t deg = __shfl_sync(kFull, word, 0);
 #ifdef HB_DEBUG_BOUNDS
         if (deg >= p.stride) { p.ctl[5] = ckey; p.ctl[6] = X; p.ctl[7] = (uint32_t)g | (ci < 0 ? 0x100u : 0u) | (b.size << 16); }
 #endif
-        HB_CHK(deg < p.stride, 3, deg);
+        HB_CHK(p.rowoff || deg < p.stride, 3, deg);
         E += deg;
         if (vcount + deg > vlimit) { status = 1; break; }
         for (uint32_t base = 0; base <= deg; base += 32) {
@@ -319,119 +323,41 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 6) hnsw_search_kernel(con
   }
 }
 
-// ---------------------------------------------------------------------------------------------
-// Fast path (ef <= 256): beam in registers, recently-seen cache in shared memory (beam.cuh).
-// Queries whose boundary-tie stack overflows are flagged and rerun on the large-capacity kernel above.
-// ---------------------------------------------------------------------------------------------
-constexpr uint32_t kFastSpillCap = 64;
-
-// resident CTAs per SM the register allocation aims for: 8 (64 registers) while the beam is one or two registers per
-// lane, 7 (72) above -- measured on B200 with the BeamHeap container: ef=64 6.80 vs 6.53 M QPS, ef=128 3.43 vs 3.63
-#ifndef HB_MIN_BLOCKS
-#define HB_MIN_BLOCKS(R) ((R) <= 2 ? 8 : 7)
-#endif
-// beam container of the query path: BeamHeap (unsorted, REDUX min/max) or BeamRegs (sorted array) -- same results
-#ifndef HB_BEAM
-#define HB_BEAM BeamHeap
-#endif
-template <int R>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS(R)) hnsw_search_fast_kernel(const SearchParams p, uint32_t cache_log2) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const size_t per_warp = warp_scratch_bytes(cache_log2) + kFastSpillCap * 4;
-  unsigned char* mine = smem_raw + wib * per_warp;
-  const WarpScratch ws = make_warp_scratch(mine, cache_log2);
-  uint32_t* const spill = ws.ids + kIdsCap;
-  const GraphView gv{p.sk, p.adj, p.stride};
-  const uint32_t sub = lane & 7u;
-
-  for (;;) {
-    uint32_t qi = 0;
-    if (lane == 0) qi = atomicAdd(p.ctl, 1u);
-    qi = __shfl_sync(kFullMask, qi, 0);
-    if (qi >= p.nq) break;
-    const uint32_t q = p.qmap ? p.qmap[qi] : qi;
-    const uint4 qv = __ldg(p.queries + (size_t)q * 8 + sub);
-#ifdef HB_DIAG_TIME
-    unsigned long long t_start;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
-#endif
-    cache_clear(ws);
-
-    SearchCounters c;
-    uint32_t status = 0;
-    uint32_t cur = p.ep_gid;
-    HB_BEAM<R> b;
-    for (int g = (int)p.n_upper; g >= 0 && status == 0; --g) {
-      const uint32_t ef = (g == 0) ? p.ef : 1u;  // hnsw.rs:286 (ef = 1 above the base)
-      beam_search(gv, qv, ef, cur, ws, spill, kFastSpillCap, b, c, status);
-      b.sort_prefix(g > 0 ? 1u : p.k);  // pop_min() above the base, drain_asc().take(k) at the base
-      if (g > 0 && status == 0) cur = __ldg(p.down + (bm_key(b.at(0)) - p.n_base));  // hnsw.rs:288-292 (.point.1)
-    }
-
-    // ---- drain_asc().take(k) (+ Indexes::search padding) ----
-    const uint32_t nres = status ? 0u : min(b.size, p.k);
-    const uint64_t first = b.at(0);
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const uint32_t j = b.sorted_index(r);
-      if (j < nres) {
-        p.keys[(size_t)q * p.k + j] = bm_key(b.w[r]);
-        p.dists[(size_t)q * p.k + j] = bm_dist(b.w[r]);
-      }
-    }
-    for (uint32_t j = nres + lane; j < p.k; j += 32) {
-      const bool pad = (p.flags & HB_PAD_LIKE_CLI) && nres;
-      p.keys[(size_t)q * p.k + j] = pad ? bm_key(first) : 0;
-      p.dists[(size_t)q * p.k + j] = pad ? bm_dist(first) : 0;
-    }
-    if (lane == 0) {
-      p.found[q] = nres;
-      p.qstatus[q] = status;
-      if (status) atomicOr(p.ctl + 1, 1u);
-#ifdef HB_DIAG_TIME
-      // diagnostics build: (start ns, end ns, warp slot, X) instead of the work counters
-      unsigned long long t_end;
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
-      if (p.counters) p.counters[q] = make_uint4((uint32_t)t_start, (uint32_t)t_end, blockIdx.x * kWarpsPerBlock + wib, c.X);
-#else
-      if (p.counters) p.counters[q] = make_uint4(c.X, c.E, c.V, c.A);
-#endif
-    }
-    __syncwarp();
-  }
-}
-
 struct FastLaunch {
   void (*kernel)(const SearchParams, uint32_t);
 };
-FastLaunch fast_kernel_for(uint32_t ef) {
-  if (ef <= 32) return {hnsw_search_fast_kernel<1>};
-  if (ef <= 64) return {hnsw_search_fast_kernel<2>};
-  if (ef <= 128) return {hnsw_search_fast_kernel<4>};
-  return {hnsw_search_fast_kernel<8>};
-}
-
 
 // ---------------------------------------------------------------------------------------------
-// Fast path, second generation (beam2.cuh): split 32-bit beam registers, register gather with 4 lanes per sketch row,
-// recently-seen cache with 16-bit tags.  Same persistent-warp structure and the same results as the kernel above.
+// Fast path (ef <= 256; beam2.cuh): beam in split 32-bit registers, register gather with 4 lanes per sketch row,
+// recently-seen cache with 16-bit tags.  Queries whose boundary-tie stack overflows are flagged and rerun on the
+// large-capacity kernel above.
 // ---------------------------------------------------------------------------------------------
+// Resident CTAs per SM and entries (log2) of the recently-seen cache per warp, by beam size.  Measured on B200 (10 M
+// points, 10 k queries; profiles/r02d_ab_gather_variants.log, r02e_ab_occupancy_rowahead_compact.log):
+//   ef <= 64 (R <= 2, 56 registers): 9 CTAs with a 512-entry cache beat 8 CTAs with 1 024 entries (8.6-8.7 against
+//   8.3-8.5 M queries/s) although the smaller cache re-evaluates more nodes (V 3 094 against 2 814; the reference's
+//   exact visited set: 2 474) -- the kernel is bound by memory latency, and one more CTA of warps hides more of it;
+//   ef > 64 (R >= 4, 72 registers -> 7 CTAs whatever the cache): the 1 024-entry cache (ef = 128: 4.8 against 4.2).
+// Compile-time so that every shared-memory address folds.
 #ifndef HB_MB2
-#define HB_MB2 8
+#define HB_MB2 9
 #endif
 #define HB_MIN_BLOCKS2(R) ((R) <= 2 ? HB_MB2 : (HB_MB2 < 7 ? HB_MB2 : 7))
-// entries (log2) of the recently-seen cache per warp: compile-time so that every shared-memory address folds
 #ifndef HB_CACHE2_LOG2
-#define HB_CACHE2_LOG2 11
+#define HB_CACHE2_LOG2 9
 #endif
-template <bool TAG16>
-__host__ __device__ constexpr uint32_t cache2_log2() { return TAG16 ? HB_CACHE2_LOG2 : HB_CACHE2_LOG2 - 1; }  // same bytes either way
+#ifndef HB_CACHE2_LOG2_BIG
+#define HB_CACHE2_LOG2_BIG 10
+#endif
+template <bool TAG16, int R>
+__host__ __device__ constexpr uint32_t cache2_log2() {
+  return (R <= 2 ? HB_CACHE2_LOG2 : HB_CACHE2_LOG2_BIG) - (TAG16 ? 0 : 1);  // full ids: half the entries in the same bytes
+}
 
 template <int R, bool TAG16, bool COUNT>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS2(R)) hnsw_search_v2_kernel(const SearchParams p, uint32_t) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  constexpr uint32_t cache_log2 = cache2_log2<TAG16>();
+  constexpr uint32_t cache_log2 = cache2_log2<TAG16, R>();
   const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   unsigned char* mine = smem_raw + wib * warp_scratch2_bytes<TAG16>(cache_log2);
   WarpScratch2<TAG16> ws;
@@ -440,7 +366,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS2(R)) hnsw_s
   ws.spill = ws.ids + kIdsWords2;
   unsigned char* const cache_mem = mine + kStageBytes2 + (kIdsWords2 + kSpillCap2) * 4;
   ws.cache.init(cache_mem, cache_log2);
-  const GraphView gv{p.sk, p.adj, p.stride};
+  const GraphView gv{p.sk, p.adj, p.stride, p.rowoff};
 
   for (;;) {
     uint32_t qi = 0;
@@ -503,14 +429,25 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS2(R)) hnsw_s
   }
 }
 
-template <bool TAG16, bool COUNT>
-FastLaunch v2_kernel_for(uint32_t ef) {
+struct FastChoice {
   FastLaunch fl;
-  if (ef <= 32) fl.kernel = hnsw_search_v2_kernel<1, TAG16, COUNT>;
-  else if (ef <= 64) fl.kernel = hnsw_search_v2_kernel<2, TAG16, COUNT>;
-  else if (ef <= 128) fl.kernel = hnsw_search_v2_kernel<4, TAG16, COUNT>;
-  else fl.kernel = hnsw_search_v2_kernel<8, TAG16, COUNT>;
-  return fl;
+  size_t smem;
+  uint32_t cache_log2;
+};
+template <int R, bool TAG16>
+FastChoice v2_choice(bool count) {
+  FastChoice c;
+  c.fl.kernel = count ? hnsw_search_v2_kernel<R, TAG16, true> : hnsw_search_v2_kernel<R, TAG16, false>;
+  c.cache_log2 = cache2_log2<TAG16, R>();
+  c.smem = (size_t)kWarpsPerBlock * warp_scratch2_bytes<TAG16>(c.cache_log2);
+  return c;
+}
+template <bool TAG16>
+FastChoice v2_choice_for(uint32_t ef, bool count) {
+  if (ef <= 32) return v2_choice<1, TAG16>(count);
+  if (ef <= 64) return v2_choice<2, TAG16>(count);
+  if (ef <= 128) return v2_choice<4, TAG16>(count);
+  return v2_choice<8, TAG16>(count);
 }
 
 uint32_t ceil_log2(uint64_t x) {
@@ -589,25 +526,11 @@ double timed_launch(SearchWorkspace& ws, cudaStream_t stream, uint32_t* h_ctl, s
   return ms;
 }
 
-struct FastChoice {
-  FastLaunch fl;
-  size_t smem;
-};
-// which ef <= 256 kernel serves this index: the v2 kernel with 16-bit cache tags while they are exact for n_total,
-// with full ids above; HB_SEARCH_V1=1 selects the round-1 kernel (kept for A/B timing)
-FastChoice choose_fast(const Index& idx, uint32_t ef, bool count, uint32_t& cache_log2) {
-  static const bool v1 = std::getenv("HB_SEARCH_V1") != nullptr;
-  if (v1) {
-    static const int env_cache = std::getenv("HB_CACHE_LOG2") ? std::atoi(std::getenv("HB_CACHE_LOG2")) : 0;
-    cache_log2 = env_cache >= 5 && env_cache <= 13 ? (uint32_t)env_cache : 9u;
-    return {fast_kernel_for(ef), (size_t)kWarpsPerBlock * (warp_scratch_bytes(cache_log2) + kFastSpillCap * 4)};
-  }
-  if (idx.n_total <= SeenCache<true>::max_ids(cache2_log2<true>())) {
-    cache_log2 = cache2_log2<true>();
-    return {count ? v2_kernel_for<true, true>(ef) : v2_kernel_for<true, false>(ef), (size_t)kWarpsPerBlock * warp_scratch2_bytes<true>(cache_log2)};
-  }
-  cache_log2 = cache2_log2<false>();
-  return {count ? v2_kernel_for<false, true>(ef) : v2_kernel_for<false, false>(ef), (size_t)kWarpsPerBlock * warp_scratch2_bytes<false>(cache_log2)};
+// which ef <= 256 kernel serves this index: 16-bit cache tags while they are exact for n_total, full ids above
+FastChoice choose_fast(const Index& idx, uint32_t ef, bool count) {
+  const FastChoice tagged = v2_choice_for<true>(ef, count);
+  if (idx.n_total <= SeenCache<true>::max_ids(tagged.cache_log2)) return tagged;
+  return v2_choice_for<false>(ef, count);
 }
 
 }  // namespace
@@ -637,6 +560,7 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   SearchParams p{};
   p.sk = idx.d_sk;
   p.adj = idx.d_adj;
+  p.rowoff = idx.d_rowoff;
   p.down = idx.d_down;
   p.queries = static_cast<const uint4*>(d_queries);
   p.keys = static_cast<uint64_t*>(d_keys);
@@ -660,8 +584,7 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   // ---- fast path: beam in registers (ef <= 256) ------------------------------------------------
   static const bool force_large = std::getenv("HB_FORCE_LARGE") != nullptr;
   if (ef <= 256 && !force_large) {
-    uint32_t cache_log2 = 0;
-    const FastChoice fc = choose_fast(idx, ef, d_counters != nullptr, cache_log2);
+    const FastChoice fc = choose_fast(idx, ef, d_counters != nullptr);
     HB_CUDA(cudaFuncSetAttribute(fc.fl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fc.smem));
     int fbps = 0;
     HB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fbps, fc.fl.kernel, kWarpsPerBlock * 32, fc.smem));
@@ -673,7 +596,7 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     p.qmap = nullptr;
     p.nq = (uint32_t)nq;
     uint32_t h_ctl[2] = {0, 0};
-    search_ms += timed_launch(ws, stream, h_ctl, 2, [&] { fc.fl.kernel<<<fblocks, kWarpsPerBlock * 32, fc.smem, stream>>>(p, cache_log2); });
+    search_ms += timed_launch(ws, stream, h_ctl, 2, [&] { fc.fl.kernel<<<fblocks, kWarpsPerBlock * 32, fc.smem, stream>>>(p, fc.cache_log2); });
     if (!h_ctl[1]) {
       idx.last_search_ms = search_ms;
       return;

@@ -155,6 +155,11 @@ class Index:
         check(_lib.lib().hb_index_graph_export(self._h, g, _p(sk), _p(down), _p(off), _p(ids)))
         return {"sketches": sk, "down": down, "off": off, "ids": ids}
 
+    def compact(self):
+        """Line-granular adjacency rows + offsets instead of fixed-stride rows (hb_index_compact): same results, ~5x less HBM."""
+        check(_lib.lib().hb_index_compact(self._h))
+        return self
+
     def write_index(self, path: str):
         """write_index (cli/src/main.rs:236-248)."""
         check(_lib.lib().hb_index_save_idx(self._h, os.fsencode(path)))

@@ -99,6 +99,7 @@ extern "C" {
     pub fn hb_index_set_attrs(idx: *mut hb_index, buildtime: c_double, params: *const c_char) -> c_int;
     pub fn hb_index_set_format_size(idx: *mut hb_index, format_size: c_int) -> c_int;
     pub fn hb_index_get_attrs(idx: *const hb_index, format_size: *mut c_int, size: *mut u64, buildtime: *mut c_double, querytime: *mut c_double, data: *mut c_char, data_cap: u64, params: *mut c_char, params_cap: u64) -> c_int;
+    pub fn hb_index_compact(idx: *mut hb_index) -> c_int;
     pub fn hb_index_free(idx: *mut hb_index);
     pub fn hb_index_size(idx: *const hb_index) -> u64;
     pub fn hb_index_get_info(idx: *const hb_index, info: *mut hb_index_info) -> c_int;

@@ -416,3 +416,55 @@ def test_knns_pinned_buffers_used_in_place(hb, oracle):
     assert np.array_equal(hf.numpy().view(np.uint32), of)
     gk, gd, gf = hidx.knns_arrays(q, k, ef)                              # pageable numpy buffers: staged copies
     assert np.array_equal(gk, ok) and np.array_equal(gd, od) and np.array_equal(gf, of)
+
+
+def test_compact_layout_returns_the_same_rows(hb, oracle):
+    """hb_index_compact: line-granular adjacency rows + offsets instead of fixed-stride rows -- a layout change only."""
+    data = oracle.synth(20000, 91)
+    q = oracle.synth(300, 92)
+    oidx = oracle.build(data, "hnsw", efc=48, m=12, M=96, parallel=False)   # hub rows longer than one two-line segment
+    hidx = _to_gpu(hb, oidx)
+    before = hidx.info().device_bytes
+    assert hidx.info().row_stride >= 64
+    hidx.compact()
+    inf = hidx.info()
+    assert inf.row_stride == 0 and inf.device_bytes < before
+    for k, ef in ((10, 64), (10, 16), (100, 256), (10, 300)):      # both kernels (ef <= 256 and the large-capacity one)
+        _assert_same(hidx, oidx, q, k, ef)
+    hidx.compact()                                                    # idempotent
+    _assert_same(hidx, oidx, q, 10, 64)
+    # a built index compacts too
+    b = hb.build_hnsw(data, efc=48, m=12, M=48, serial_prefix=2000)
+    k0, d0, f0 = b.knns_arrays(q, 10, 64)
+    b.compact()
+    k1, d1, f1 = b.knns_arrays(q, 10, 64)
+    assert np.array_equal(k0, k1) and np.array_equal(d0, d1) and np.array_equal(f0, f1)
+
+
+def test_parity_at_one_million_points(hb, oracle):
+    """Full-size behaviour inside -m gpu: a 1 M-point index (device builder, reference parameters), every query of a
+    2 000-query batch identical to the oracle's on the same graph (ids, distances, X/E/A), plus the large-capacity path
+    (ef = 1000: exact visited tables sized per call on the caller's stream) on a 10 k batch through hb_knns."""
+    import torch
+    n, nq = 1_000_000, 10_000
+    d = torch.empty((n, 16), dtype=torch.int64, device="cuda")
+    hb.synth_sketches(d.data_ptr(), n, 1003)
+    dq = torch.empty((nq, 16), dtype=torch.int64, device="cuda")
+    hb.synth_sketches(dq.data_ptr(), nq, 1004)
+    torch.cuda.synchronize()
+    data, q = d.cpu().numpy().view(np.uint64), dq.cpu().numpy().view(np.uint64)
+    del d, dq
+    hidx = hb.build_hnsw(data, efc=96, m=24, M=256, rayon_threads=16, keep_host=True)
+    inf = hidx.info()
+    assert inf.size == n and inf.build_dropped_appends == 0
+    oidx = oracle.from_parts("hnsw", [hidx.graph(g) for g in range(inf.n_graphs)], inf.entry_point)
+    _assert_same(hidx, oidx, q[:2000], 10, 64)
+    _assert_same(hidx, oidx, q[:500], 10, 256)
+    # ef = 1000 over the whole batch on pageable host buffers: first use of the visited tables (memset on the call's stream)
+    gk, gd, gf = hidx.knns_arrays(q, 10, 1000)
+    ok, od, of = oidx.knns(q[:300], 10, 1000)
+    assert np.array_equal(gk[:300], ok) and np.array_equal(gd[:300], od) and np.array_equal(gf[:300], of)
+    assert (gf == 10).all() and (np.diff(gd.astype(np.int64), axis=1) >= 0).all()
+    # and again after compaction of the adjacency
+    hidx.compact()
+    _assert_same(hidx, oidx, q[:500], 10, 64)
