@@ -270,6 +270,8 @@ def split(n, world, r):
 
 def main():
     a = parse()
+    # NCCL writes its version banner (NCCL_DEBUG=VERSION/INFO) to stdout by default: keep stdout for the one JSON line
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     if a.impl == "reference":
         return run_reference(a, int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
     R = Rig(a)
@@ -413,6 +415,34 @@ def run_extras(R, a, idx, dq, gpu_keys, gt_keys):
                         "identical_to_unsplit_ids": same,
                         "note": "one launch per GPU over its contiguous slice; below one wave per GPU the limiter is the per-query "
                                 "dependent chain, not a collective (there is none)"}
+    # ---- two concurrent callers per GPU, each with its own 10 k batch on its own stream (Index::search is Sync, mod.rs:21-43;
+    #      per-call workspaces in the library): the second batch's head fills the first one's tail ----------------------
+    import threading
+    n_callers = 2
+    streams = [torch.cuda.Stream() for _ in range(n_callers)]
+    bufs = [(torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda"), torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda"),
+             torch.empty(a.nq, dtype=torch.int32, device="cuda")) for _ in range(n_callers)]
+    torch.cuda.synchronize()
+
+    def caller(i, reps):
+        k_, d_, f_ = bufs[i]
+        for _ in range(reps):
+            R._lib.check(R.lib.hb_knns_device(h, dq.data_ptr(), a.nq, a.k, a.ef, 0, k_.data_ptr(), d_.data_ptr(), f_.data_ptr(), None,
+                                              streams[i].cuda_stream))
+
+    def concurrent(reps):
+        th = [threading.Thread(target=caller, args=(i, reps)) for i in range(n_callers)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+        torch.cuda.synchronize()
+    concurrent(3)
+    R.barrier()
+    t0 = time.perf_counter()
+    concurrent(a.steps)
+    conc_s = R.max_over_ranks(time.perf_counter() - t0)
+    out["concurrent_callers"] = {"callers_per_gpu": n_callers, "batches_per_caller": a.steps, "qps": world * n_callers * a.steps * a.nq / conc_s,
+                                 "identical_ids": bool(np.array_equal(bufs[1][0].cpu().numpy().view(u64), gpu_keys)),
+                                 "note": "wall clock over both callers; each call is still one launch + one stream synchronise"}
     # ---- saturating batch: the 10 k queries tiled x100 = 1 M, split N ways ------------------------------------
     tile = 100
     nq_sat = a.nq * tile
