@@ -48,6 +48,10 @@ struct GraphView {
   const uint32_t* adj;   // n_total rows of `stride` words: [0] = degree, then neighbour gids in canonical order
   uint32_t stride;
   const uint32_t* rowoff;  // compact layout: first 128-B line of every row (nullptr: fixed stride)
+#ifdef HB_DEBUG_BOUNDS
+  uint32_t* dbg;       // [0] first failed check (0 = none), [1] offending value, [2] query
+  uint32_t n_total;
+#endif
   __device__ __forceinline__ const uint32_t* row(uint32_t gid) const {
     return rowoff ? adj + (size_t)__ldg(rowoff + gid) * 32 : adj + (size_t)gid * stride;
   }

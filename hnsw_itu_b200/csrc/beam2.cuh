@@ -363,6 +363,22 @@ __host__ __device__ constexpr size_t warp_scratch2_bytes(uint32_t entries_log2) 
   return SeenCache<TAG16>::bytes(entries_log2) + (size_t)(kIdsWords2 + kSpillCap2) * 4 + kStageBytes2;
 }
 
+// -DHB_DEBUG_BOUNDS: every gid, degree and staged count is checked before it is used as an address; the first failure is
+// recorded (code, value) and the query ends with status 3.  compute-sanitizer is not available on the GPU pool, this build
+// run through the parity tests is the memory-safety evidence (profiles/r02*_debug_bounds*.log).
+#ifdef HB_DEBUG_BOUNDS
+#define HB_CHK2(cond, code, val)                                              \
+  do {                                                                        \
+    if (!__all_sync(kFullMask, (cond))) {                                     \
+      if (lane == 0 && atomicCAS(gv.dbg, 0u, (uint32_t)(code)) == 0u) gv.dbg[1] = (uint32_t)(val); \
+      status = 3;                                                             \
+      return;                                                                 \
+    }                                                                         \
+  } while (0)
+#else
+#define HB_CHK2(cond, code, val) do {} while (0)
+#endif
+
 // nsw::search(graph, q, ef, ep) (nsw.rs:133-184) on the graph that contains gid `ep`.  On return b holds w.
 // status != 0: the boundary-tie stack overflowed (the caller reruns the query on the large-capacity kernel).
 // COUNT = false drops the X/E/V/A work counters (four registers and their updates) from the timed path.
@@ -371,6 +387,7 @@ __device__ __forceinline__ void beam_search2(const GraphView& gv, const QueryReg
                                              const WarpScratch2<TAG16>& ws, BeamSplit<R>& b, SearchCounters& c, uint32_t& status) {
   const uint32_t lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
+  HB_CHK2(ep < gv.n_total, 11, ep);
   {
     const uint32_t d0 = hamming_one(gv.sk, ep, q);  // nsw.rs:140-141
     if (lane == 0) ws.cache.test_and_set(ep);        // nsw.rs:143-144
@@ -392,12 +409,14 @@ __device__ __forceinline__ void beam_search2(const GraphView& gv, const QueryReg
       }
     }
     if (COUNT) ++c.X;
+    HB_CHK2(ckey < gv.n_total, 12, ckey);
     // ---- for e in graph.neighborhood(c.key)  (nsw.rs:156) ----
     const uint32_t* row = gv.row(ckey);
     uint32_t w0, w1;
     w0 = __ldg(row + lane);
     w1 = __ldg(row + 32 + lane);
     const uint32_t deg = __shfl_sync(kFullMask, w0, 0);
+    HB_CHK2(gv.rowoff ? deg < 65536u : deg < gv.stride, 13, deg);
     if (COUNT) c.E += deg;
     for (uint32_t base = 0; base <= deg; base += 64) {
       // rows longer than one segment (hubs): pull the next segment's two lines into L2 while this one is worked on
@@ -418,6 +437,7 @@ __device__ __forceinline__ void beam_search2(const GraphView& gv, const QueryReg
         if (isnew) ws.ids[n_new + __popc(nm & lt_mask)] = w1;
         n_new += __popc(nm);
       }
+      HB_CHK2(n_new <= kIdsCap, 14, n_new);
       if (lane < kIdsPad) ws.ids[n_new + lane] = ckey;  // padding rows: any valid gid
       if (COUNT) c.V += n_new;
       __syncwarp();
@@ -427,6 +447,7 @@ __device__ __forceinline__ void beam_search2(const GraphView& gv, const QueryReg
       for (uint32_t g0 = 0; g0 < n_new; g0 += 32) {
         const uint32_t n = min(32u, n_new - g0);
         const uint32_t myid = ws.ids[g0 + lane];
+        HB_CHK2(lane >= n || myid < gv.n_total, 15, myid);
         // distance_fn(point, query) for the group (nsw.rs:164-165)
 #if HB_GATHER2 == 1
         const uint32_t myd = gather_finish(n, q, ws.stage);

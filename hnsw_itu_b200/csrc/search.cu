@@ -366,7 +366,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, HB_MIN_BLOCKS2(R)) hnsw_s
   ws.spill = ws.ids + kIdsWords2;
   unsigned char* const cache_mem = mine + kStageBytes2 + (kIdsWords2 + kSpillCap2) * 4;
   ws.cache.init(cache_mem, cache_log2);
+#ifdef HB_DEBUG_BOUNDS
+  const GraphView gv{p.sk, p.adj, p.stride, p.rowoff, p.ctl + 2, p.n_total};
+#else
   const GraphView gv{p.sk, p.adj, p.stride, p.rowoff};
+#endif
 
   for (;;) {
     uint32_t qi = 0;
@@ -595,8 +599,11 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
     p.qstatus = ws.qstatus;
     p.qmap = nullptr;
     p.nq = (uint32_t)nq;
-    uint32_t h_ctl[2] = {0, 0};
-    search_ms += timed_launch(ws, stream, h_ctl, 2, [&] { fc.fl.kernel<<<fblocks, kWarpsPerBlock * 32, fc.smem, stream>>>(p, fc.cache_log2); });
+    uint32_t h_ctl[4] = {0, 0, 0, 0};
+    search_ms += timed_launch(ws, stream, h_ctl, 4, [&] { fc.fl.kernel<<<fblocks, kWarpsPerBlock * 32, fc.smem, stream>>>(p, fc.cache_log2); });
+#ifdef HB_DEBUG_BOUNDS
+    HB_REQUIRE(h_ctl[2] == 0, HB_ERR_INTERNAL, "bounds check " + std::to_string(h_ctl[2]) + " failed in the ef <= 256 kernel, value " + std::to_string(h_ctl[3]));
+#endif
     if (!h_ctl[1]) {
       idx.last_search_ms = search_ms;
       return;
