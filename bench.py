@@ -65,6 +65,7 @@ def parse():
     ap.add_argument("--no-extras", action="store_true", help="skip the strong / sweep / sharded legs (headline only)")
     ap.add_argument("--no-100m", action="store_true", help="skip configs[4] (100 M sharded HNSW) at N = 8")
     ap.add_argument("--shard-rows", type=int, default=12_500_000, help="rows per shard of configs[4]")
+    ap.add_argument("--force-sharded-hnsw", action="store_true", help="run the configs[4] leg at any N (default: N = 8 only)")
     return ap.parse_args()
 
 
@@ -469,12 +470,13 @@ def run_extras(R, a, idx, dq, gpu_keys, gt_keys):
     torch.cuda.empty_cache()
 
     # ---- configs[4]: 100 M rows as N shards, one HNSW per shard, sharded search + all-gather + exact merge ------
-    if world == 8 and not a.no_100m:
+    if (world == 8 or a.force_sharded_hnsw) and not a.no_100m:
         rows = a.shard_rows
         off = rank * rows
         d_shard = synth_on_device(hb, torch, rows, 1003, start=off)
         t0 = time.time()
-        sidx = hb.build_hnsw(d_shard.cpu().numpy().view(u64), efc=a.efc, m=a.m, M=a.M, rayon_threads=a.rayon_threads, keep_host=False)
+        sidx = hb.build_hnsw(d_shard.cpu().numpy().view(u64), efc=a.efc, m=a.m, M=a.M, rayon_threads=a.rayon_threads, keep_host=False,
+                             device=R.local_rank)
         R.barrier()
         build_s = time.time() - t0
         d_gt = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")

@@ -237,7 +237,10 @@ int hb_index_set_format_size(hb_index* h, int format_size) {
   return guarded([&] { as_index(h)->attrs.format_size = format_size != 0; });
 }
 
-void hb_index_free(hb_index* h) { delete reinterpret_cast<Index*>(h); }
+void hb_index_free(hb_index* h) {
+  DeviceRestore restore;
+  delete reinterpret_cast<Index*>(h);
+}
 
 uint64_t hb_index_size(const hb_index* h) { return h ? reinterpret_cast<const Index*>(h)->n_base : 0; }
 

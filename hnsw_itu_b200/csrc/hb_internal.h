@@ -37,9 +37,26 @@ void count_launches(uint64_t n = 1);  // every kernel launch of the library is c
     if (!(cond)) throw hb::Error((code), (msg)); \
   } while (0)
 
-// every extern "C" entry point runs its body through this: exceptions become hb_status codes + hb_last_error()
+// every extern "C" entry point runs its body through this: exceptions become hb_status codes + hb_last_error(), and the
+// caller's current CUDA device is put back if the call changed it (the entry points cudaSetDevice to the index's /
+// communicator's device; a host that keeps its own notion of "current device", like PyTorch, must not see that)
+struct DeviceRestore {
+  int prev = -1;
+  DeviceRestore() {
+    if (cudaGetDevice(&prev) != cudaSuccess) {
+      cudaGetLastError();
+      prev = -1;
+    }
+  }
+  ~DeviceRestore() {
+    int cur = -1;
+    if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+  }
+};
+
 template <class F>
 int guarded(F&& f) {
+  DeviceRestore restore;
   try {
     f();
     return HB_OK;

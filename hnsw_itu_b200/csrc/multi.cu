@@ -457,7 +457,10 @@ int hb_comm_init_rank(const uint8_t id[HB_COMM_ID_BYTES], int nranks, int rank, 
   });
 }
 
-void hb_comm_free(hb_comm* c) { delete reinterpret_cast<Comm*>(c); }
+void hb_comm_free(hb_comm* c) {
+  DeviceRestore restore;
+  delete reinterpret_cast<Comm*>(c);
+}
 
 int hb_comm_phase_ms(hb_comm* h, double ms[3]) {
   return guarded([&] {
@@ -532,7 +535,10 @@ int hb_multi_create(const int* devices, int ndev, hb_multi** out) {
   });
 }
 
-void hb_multi_free(hb_multi* h) { delete reinterpret_cast<Multi*>(h); }
+void hb_multi_free(hb_multi* h) {
+  DeviceRestore restore;
+  delete reinterpret_cast<Multi*>(h);
+}
 
 int hb_multi_device_count(const hb_multi* h) { return h ? reinterpret_cast<const Multi*>(h)->ndev() : 0; }
 uint64_t hb_multi_size(const hb_multi* h) { return h ? reinterpret_cast<const Multi*>(h)->n_rows : 0; }

@@ -158,3 +158,24 @@ def test_concurrent_callers_on_one_index(hb, oracle):
     [x.start() for x in th]
     [x.join() for x in th]
     assert not errors, errors
+
+
+def test_library_calls_leave_the_callers_current_device_alone(hb, oracle):
+    """Every entry point works on the device of its index / communicator and puts the caller's current device back: a
+    host with its own notion of "current device" (PyTorch allocates on cudaGetDevice()) must not see it move."""
+    if _n_devices() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch
+    torch.cuda.set_device(1)
+    data, q = oracle.synth(3000, 73), oracle.synth(40, 74)
+    idx0 = hb.build_hnsw(data, efc=32, m=8, M=32, serial_prefix=500, device=0)
+    assert torch.cuda.current_device() == 1
+    idx0.knns_arrays(q, 10, 64)
+    hb.ground_truth(data, q, 10, device=0)
+    idx0.compact()
+    assert torch.cuda.current_device() == 1
+    t = torch.empty(4, device="cuda")
+    assert t.device.index == 1
+    del idx0
+    assert torch.cuda.current_device() == 1
+    torch.cuda.set_device(0)
