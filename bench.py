@@ -263,6 +263,15 @@ class Rig:
         return full
 
 
+_T0 = time.time()
+
+
+def phase(msg):
+    """Progress on stderr (rank 0): where the wall clock of a run goes."""
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(f"[bench {time.time() - _T0:7.1f}s] {msg}", file=sys.stderr, flush=True)
+
+
 def split(n, world, r):
     """Contiguous (start, len): the reference's `-b start -l len` (cli/src/main.rs:136-140)."""
     e0, e1 = (r * n) // world, ((r + 1) * n) // world
@@ -301,12 +310,14 @@ def main():
             data = None
         del d_data
         torch.cuda.empty_cache()
+    phase(f"index built in {build_s:.1f}s")
     t_b = time.time()
     idx = R.comm.broadcast_index(idx, 0)     # hb_index_broadcast: ncclBroadcast of sketches / adjacency rows / down-links
     R.barrier()
     bcast_s = time.time() - t_b
     h = idx._h
 
+    phase(f"index replicated in {bcast_s:.1f}s")
     # ---- configs[3]: exact ground truth with the rows sharded over the ranks (also the recall reference) -------
     r0, rl = split(a.n, world, rank)
     d_shard = synth_on_device(hb, torch, rl, 1003, start=r0)
@@ -334,7 +345,14 @@ def main():
     gpu_dists = dd.cpu().numpy().view(u64).copy()
     ctr = dc.cpu().numpy().astype(np.float64)
     recall = recall_at_k(gpu_keys, gt_keys, a.k)
+    ns = min(1000, a.nq)
+    dce = torch.empty((ns, 4), dtype=torch.int32, device="cuda")
+    _lib.check(lib.hb_knns_device(h, dq.data_ptr(), ns, a.k, a.ef, _lib.HB_EXACT_VISITED, dk.data_ptr(), dd.data_ptr(), df.data_ptr(),
+                                  dce.data_ptr(), R.stream))
+    assert np.array_equal(dk[:ns].cpu().numpy().view(u64), gpu_keys[:ns]), "exact-visited kernel returned different ids"
+    v_exact = float(dce.cpu().numpy()[:, 2].mean()) * float(ctr[:, 2].mean() / ctr[:ns, 2].mean())
 
+    phase("ground truth + counted pass done")
     # ---- headline: device-resident, one 10 k batch per GPU ------------------------------------------------------
     step = R.knns_fn(h, dq_own, a.nq, a.k, a.ef, dk, dd, df)
     warm = max(a.warmup, 3)
@@ -381,6 +399,7 @@ def main():
     if rank == 0:
         assert np.array_equal(pinned["hk"].numpy().view(u64), gpu_keys), "pinned host-buffer path returned different ids"
 
+    phase("headline + e2e legs done")
     extras = {}
     if not a.no_extras:
         extras = run_extras(R, a, idx, dq, gpu_keys, gt_keys)
@@ -394,7 +413,7 @@ def main():
             R.dist.destroy_process_group()
         return
     report(R, a, idx, dict(build_s=build_s, bcast_s=bcast_s, data=data, gt_e2e_ms=gt_e2e_ms, gt_ms=gt_ms, gt_phase=gt_phase,
-                           gt_sha=gt_sha, gt_keys=gt_keys, gpu_keys=gpu_keys, gpu_dists=gpu_dists, ctr=ctr, recall=recall, kernel_ms=kernel_ms,
+                           gt_sha=gt_sha, gt_keys=gt_keys, v_exact=v_exact, gpu_keys=gpu_keys, gpu_dists=gpu_dists, ctr=ctr, recall=recall, kernel_ms=kernel_ms,
                            total_ms=total_ms, launches=launches, clocks=clocks, e2e_pageable_s=e2e_pageable_s,
                            e2e_pinned_s=e2e_pinned_s, warm=warm, want_cpu=want_cpu, dq=dq, extras=extras))
     if world > 1:
@@ -469,6 +488,7 @@ def run_extras(R, a, idx, dq, gpu_keys, gt_keys):
     del dq_sat, sk, sd, sf
     torch.cuda.empty_cache()
 
+    phase("split / concurrent / saturating / ef sweep done")
     # ---- configs[4]: 100 M rows as N shards, one HNSW per shard, sharded search + all-gather + exact merge ------
     if (world == 8 or a.force_sharded_hnsw) and not a.no_100m:
         rows = a.shard_rows
@@ -499,6 +519,7 @@ def run_extras(R, a, idx, dq, gpu_keys, gt_keys):
                     "ncclAllGather of nq*k packed u64 per rank + exact (distance, key) merge inside libhnswb200"}
         del sidx, d_shard
         torch.cuda.empty_cache()
+        phase("sharded HNSW leg done")
     return out
 
 
@@ -544,17 +565,10 @@ def report(R, a, idx, s):
     X, E, Vgpu = ctr[:, 0].mean(), ctr[:, 1].mean(), ctr[:, 2].mean()
     v_note = "oracle |visited| over the whole batch"
     if v_alg is None:
-        # no full CPU leg (N > 1 or --no-cpu-baseline): the reference's |visited| from the oracle on a 500-query sample,
-        # scaled by the GPU's own evaluation counts (the GPU re-evaluates nodes its recently-seen cache forgot)
-        try:
-            orc, o = native_oracle()
-            oidx = oracle_index_from(idx, o)
-            ns = min(500, a.nq)
-            _, _, _, oc = oidx.knns(q[:ns], a.k, a.ef, counters=True, threads=cores)
-            v_alg = float(oc[:, 2].mean()) * float(Vgpu / ctr[:ns, 2].mean())
-            v_note = f"oracle |visited| on the first {ns} queries, scaled to the batch by the GPU's evaluation counts"
-        except Exception as e:  # host graphs not kept: fall back to the GPU's (larger) count and say so
-            v_note = f"GPU distance evaluations (oracle sample unavailable: {type(e).__name__}); overstates the algorithmic bytes"
+        # no CPU leg (N > 1 or --no-cpu-baseline): the reference's |visited| measured on the device -- the large-capacity
+        # kernel keeps the exact visited set (HB_EXACT_VISITED), so its V counter is the oracle's (asserted in the GPU tests)
+        v_alg = s.get("v_exact")
+        v_note = "exact visited set on the device (HB_EXACT_VISITED) over the first 1000 queries, scaled to the batch by the GPU's evaluation counts"
     V = v_alg if v_alg is not None else Vgpu
     bytes_q = 128 * V + 4 * E + 8 * X + 128 + 16 * a.k
     k_ms = float(np.mean(s["kernel_ms"]))
@@ -593,7 +607,7 @@ def report(R, a, idx, s):
                    "parallelism": ("replicated index (built on rank 0, replicated GPU-to-GPU by hb_index_broadcast = ncclBroadcast inside the "
                                    "library), one query batch per GPU, no data-path collective") if world > 1 else "1 GPU",
                    "host_cores": cores,
-                   "per_query": {"expansions": X, "ids_scanned": E, "visited_reference": V, "visited_reference_source": v_note,
+                   "per_query": {"expansions": X, "ids_scanned": E, "visited_reference": V, "visited_reference_source": v_note, "visited_exact_on_device": s.get("v_exact"),
                                  "distance_evals_gpu": Vgpu}},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": kname, "kernel_ms": k_ms, "bytes_per_query": bytes_q,
@@ -619,6 +633,7 @@ def report(R, a, idx, s):
                          "frac_of_nominal_9000": tops / (9000.0 * world)}},
     }
     line.update({"strong": s["extras"]} if s["extras"] else {})
+    phase("report done")
     print(json.dumps(line), flush=True)
 
 

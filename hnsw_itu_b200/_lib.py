@@ -17,6 +17,7 @@ HB_OK = 0
 HB_ERR_INVALID, HB_ERR_IO, HB_ERR_FORMAT, HB_ERR_CUDA, HB_ERR_NO_DEVICE = 1, 2, 3, 4, 5
 HB_ERR_OOM, HB_ERR_EMPTY_RESULT, HB_ERR_UNSUPPORTED, HB_ERR_INTERNAL = 6, 7, 8, 9
 HB_PAD_LIKE_CLI = 1
+HB_EXACT_VISITED = 2
 ALGO_NAMES = ["bruteforce", "nsw", "hnsw"]
 
 _u64p = C.POINTER(C.c_uint64)
@@ -60,6 +61,25 @@ def build_library(force: bool = False) -> str:
 _lib = None
 
 
+def _prefer_bundled_nccl():
+    """libhnswb200 resolves NCCL with dlopen("libnccl.so.2") at first multi-GPU use.  In a process that also imports
+    PyTorch, both must end up with the SAME libnccl: the dynamic linker keys loaded objects by SONAME, so if the system
+    libnccl (older) were loaded first, `import torch` would later bind to it and fail on symbols it lacks.  Point the
+    library at the NCCL wheel PyTorch itself loads (site-packages/nvidia/nccl/lib) when there is one."""
+    if os.environ.get("HB_NCCL_LIB"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for base in (list(spec.submodule_search_locations) if spec and spec.submodule_search_locations else []):
+            cand = os.path.join(base, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                os.environ["HB_NCCL_LIB"] = cand
+                return
+    except Exception:
+        pass
+
+
 def lib() -> C.CDLL:
     global _lib
     if _lib is not None:
@@ -67,6 +87,7 @@ def lib() -> C.CDLL:
     if not os.path.exists(LIB_PATH):
         raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                           "(hnsw_itu_b200 has no CPU fallback)")
+    _prefer_bundled_nccl()
     L = C.CDLL(LIB_PATH)
     if os.environ.get("HB_LIB_PATH"):
         # an A/B build (tools/ab.py) may predate the newest entry points: binding a missing symbol is skipped, calling it fails

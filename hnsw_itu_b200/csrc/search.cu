@@ -587,7 +587,7 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
 
   // ---- fast path: beam in registers (ef <= 256) ------------------------------------------------
   static const bool force_large = std::getenv("HB_FORCE_LARGE") != nullptr;
-  if (ef <= 256 && !force_large) {
+  if (ef <= 256 && !force_large && !(flags & HB_EXACT_VISITED)) {
     const FastChoice fc = choose_fast(idx, ef, d_counters != nullptr);
     HB_CUDA(cudaFuncSetAttribute(fc.fl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fc.smem));
     int fbps = 0;

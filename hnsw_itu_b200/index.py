@@ -101,16 +101,18 @@ class Index:
     def algo(self) -> str:
         return _lib.ALGO_NAMES[self.info().algo]
 
-    def knns_arrays(self, queries, k: int, ef: int, pad: bool = False, counters: bool = False):
+    def knns_arrays(self, queries, k: int, ef: int, pad: bool = False, counters: bool = False, exact_visited: bool = False):
         """Batched search returning arrays: keys (nq,k) u64, dists (nq,k) u64, found (nq) u32
-        [, counters (nq,4) u32 = X,E,V,A]."""
+        [, counters (nq,4) u32 = X,E,V,A].  exact_visited: HB_EXACT_VISITED (the kernel with the reference's exact
+        visited set whatever ef is; V then equals the reference's |visited|)."""
         q = _sketches(queries)
         nq = len(q)
         keys = np.zeros((nq, k), dtype=np.uint64)
         dists = np.zeros((nq, k), dtype=np.uint64)
         found = np.zeros(nq, dtype=np.uint32)
         ctr = np.zeros((nq, 4), dtype=np.uint32) if counters else None
-        check(_lib.lib().hb_knns(self._h, _p(q), nq, k, ef, HB_PAD_LIKE_CLI if pad else 0, _p(keys), _p(dists), _p(found, _u32p),
+        check(_lib.lib().hb_knns(self._h, _p(q), nq, k, ef, (HB_PAD_LIKE_CLI if pad else 0) | (_lib.HB_EXACT_VISITED if exact_visited else 0),
+                                 _p(keys), _p(dists), _p(found, _u32p),
                                  ctr.ctypes.data_as(C.c_void_p) if counters else None))
         return (keys, dists, found, ctr) if counters else (keys, dists, found)
 

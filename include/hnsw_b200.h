@@ -51,6 +51,8 @@ typedef enum hb_algo { HB_ALGO_BRUTEFORCE = 0, HB_ALGO_NSW = 1, HB_ALGO_HNSW = 2
 
 /* flags for hb_knns / hb_search */
 #define HB_PAD_LIKE_CLI 1u /* Indexes::search: repeat the first result up to k (main.rs:467-474) */
+#define HB_EXACT_VISITED 2u /* run the kernel that keeps the reference's exact visited set (nsw.rs:143,157-161) whatever ef is:
+                              same results, slower; its dist_evals counter then equals the reference's |visited| */
 
 #define HB_MAX_EF 4096u
 #define HB_MAX_K 4096u

@@ -33,6 +33,8 @@ pub const HB_ALGO_NSW: c_int = 1;
 pub const HB_ALGO_HNSW: c_int = 2;
 /// `Indexes::search`: repeat the first result up to k (cli/src/main.rs:467-474)
 pub const HB_PAD_LIKE_CLI: u32 = 1;
+/// run the kernel with the reference's exact visited set whatever ef is (its dist_evals counter = |visited|)
+pub const HB_EXACT_VISITED: u32 = 2;
 pub const HB_MAX_EF: u32 = 4096;
 pub const HB_MAX_K: u32 = 4096;
 pub const HB_COMM_ID_BYTES: usize = 128;

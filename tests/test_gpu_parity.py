@@ -468,3 +468,15 @@ def test_parity_at_one_million_points(hb, oracle):
     # and again after compaction of the adjacency
     hidx.compact()
     _assert_same(hidx, oidx, q[:500], 10, 64)
+
+
+def test_exact_visited_flag_reproduces_the_references_visited_count(hb, oracle):
+    """HB_EXACT_VISITED: the large-capacity kernel at any ef; all four counters (X, E, V, A) equal the oracle's."""
+    data, q = oracle.synth(8000, 93), oracle.synth(200, 94)
+    oidx = oracle.build(data, "hnsw", efc=48, m=12, M=48, parallel=False)
+    hidx = _to_gpu(hb, oidx)
+    for k, ef in ((10, 64), (10, 16)):
+        ok, od, of, oc = oidx.knns(q, k, ef, counters=True)
+        gk, gd, gf, gc = hidx.knns_arrays(q, k, ef, counters=True, exact_visited=True)
+        assert np.array_equal(gk, ok) and np.array_equal(gd, od) and np.array_equal(gf, of)
+        assert np.array_equal(gc.astype(np.uint64), oc), (k, ef)
