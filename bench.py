@@ -61,6 +61,9 @@ def parse():
     ap.add_argument("--m", type=int, default=24)
     ap.add_argument("--M", type=int, default=256)
     ap.add_argument("--rayon-threads", type=int, default=16, help="stands in for rayon's thread count at build time (chunk = 32x)")
+    ap.add_argument("--index-builder", default="device", choices=["device", "reference"],
+                    help="device: hb_build_hnsw (38 s at 10 M); reference: the restated reference builder on the host cores, written as "
+                         ".idx and loaded through hb_index_load_idx (~4 min at 10 M on 16 cores; profiles/r02_refbuilt_10M.json compares the two)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the strong / sweep / sharded legs (headline only)")
     ap.add_argument("--no-100m", action="store_true", help="skip configs[4] (100 M sharded HNSW) at N = 8")
@@ -153,13 +156,25 @@ def build_index(hb, torch, a, keep_host):
     d = synth_on_device(hb, torch, a.n, 1003)
     data = d.cpu().numpy().view(np.uint64)
     t0 = time.time()
-    idx = hb.build_hnsw(data, efc=a.efc, m=a.m, M=a.M, rayon_threads=a.rayon_threads, keep_host=keep_host)
+    if a.index_builder == "reference":
+        # configs[1] "reference-built index": HNSWBuilder::extend_parallel restated (oracle), bincode .idx, read_index on the device
+        import tempfile
+        orc, o = native_oracle()
+        oidx = o.build(data, "hnsw", a.efc, a.m, a.M, True, a.rayon_threads, host_threads())
+        with tempfile.TemporaryDirectory() as tmp:
+            path = os.path.join(tmp, "reference_built.idx")
+            oidx.save_idx(path)
+            del oidx
+            idx = hb.read_index(path, device=torch.cuda.current_device(), keep_host=keep_host)
+    else:
+        idx = hb.build_hnsw(data, efc=a.efc, m=a.m, M=a.M, rayon_threads=a.rayon_threads, keep_host=keep_host,
+                            device=torch.cuda.current_device())
     return d, data, idx, time.time() - t0
 
 
 def workload_name(a):
     return (f"synthetic {a.n} x 1024-bit sketches (SimHash of a 4096-cluster latent mixture, seeds 1001-1004), {a.nq} queries per GPU, "
-            f"index m={a.m} M={a.M} efc={a.efc} built on the device, ef={a.ef} k={a.k}")
+            f"index m={a.m} M={a.M} efc={a.efc} built " + ("on the device" if a.index_builder == "device" else "by the restated reference builder on the host, loaded from its .idx") + f", ef={a.ef} k={a.k}")
 
 
 def run_reference(a, rank, world):
