@@ -313,8 +313,33 @@ __global__ void __launch_bounds__(kPruneThreads) build_prune_kernel(const BuildC
       }
       if (tid == 0) atomicAdd(c.ctr + 10, 1u);
     }
-    // rewrite the row: selection in ascending order, then this step's new nodes that were not selected
-    __shared__ uint32_t s_len;
+    // The reference re-adds the inserting point after every prune (nsw.rs:129), so this step's new nodes stay in the row
+    // even when the heuristic did not pick them -- but it prunes at EVERY overflow, one insert at a time, so its row
+    // never ends above M.  When a whole chunk lands on one row in a single step (the star of a new top layer,
+    // hnsw.rs:89-92), selection + new nodes would stay above M here: keep only the latest new nodes (largest ids = last
+    // in the reference's chunk order) up to M in total, and unlink the others like any dropped neighbour.
+    __shared__ uint32_t s_len, s_cnt;
+    uint32_t new_keep_from = new_lo;  // unselected new nodes with id >= this stay
+    {
+      const uint32_t budget = c.M > ns ? c.M - ns : 0u;
+      uint32_t lo_t = new_lo, hi_t = new_hi;  // smallest T in [new_lo, new_hi] with count(unselected new id >= T) <= budget
+      while (lo_t < hi_t) {
+        const uint32_t mid = lo_t + ((hi_t - lo_t) >> 1);
+        if (tid == 0) s_cnt = 0;
+        __syncthreads();
+        uint32_t mine = 0;
+        for (uint32_t r = tid; r < n_valid; r += kPruneThreads) {
+          const uint32_t id = (uint32_t)(keys[r] >> 9);
+          mine += (!chosen[r] && id >= mid && id < new_hi) ? 1u : 0u;
+        }
+        if (mine) atomicAdd(&s_cnt, mine);
+        __syncthreads();
+        const uint32_t cnt = s_cnt;
+        __syncthreads();
+        if (cnt <= budget) hi_t = mid; else lo_t = mid + 1;
+      }
+      new_keep_from = lo_t;
+    }
     if (tid == 0) s_len = 0;
     __syncthreads();
     if (warp == 0) {  // ordered compaction of the chosen ranks
@@ -329,7 +354,7 @@ __global__ void __launch_bounds__(kPruneThreads) build_prune_kernel(const BuildC
       for (uint32_t r0 = 0; r0 < n_valid; r0 += 32) {
         const uint32_t r = r0 + lane;
         const uint32_t id = r < n_valid ? (uint32_t)(keys[r] >> 9) : 0u;
-        const bool take = r < n_valid && !chosen[r] && id >= new_lo && id < new_hi;
+        const bool take = r < n_valid && !chosen[r] && id >= new_keep_from && id < new_hi;
         const uint32_t mk = __ballot_sync(kFullMask, take);
         if (take) row[1 + len + __popc(mk & ((1u << lane) - 1u))] = id;
         len += __popc(mk);
@@ -339,7 +364,7 @@ __global__ void __launch_bounds__(kPruneThreads) build_prune_kernel(const BuildC
       // dropped on this side: e must leave row x as well
       for (uint32_t r = tid - 32; r < n_valid; r += kPruneThreads - 32) {
         const uint32_t id = (uint32_t)(keys[r] >> 9);
-        if (!chosen[r] && !(id >= new_lo && id < new_hi)) {
+        if (!chosen[r] && !(id >= new_keep_from && id < new_hi)) {
           const uint32_t q = atomicAdd(c.ctr + 1, 1u);
           if (q < c.req_cap) { c.req[2 * (size_t)q] = id; c.req[2 * (size_t)q + 1] = e; } else atomicOr(c.ctr + 9, kErrReq);
         }
