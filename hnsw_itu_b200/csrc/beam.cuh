@@ -1,4 +1,6 @@
-// beam.cuh -- warp-level building blocks of the batched beam search (sm_100a).
+// beam.cuh -- warp-level building blocks of the batched beam search (sm_100a), first generation.  The query path moved to
+// beam2.cuh in round 2 (split 32-bit beam registers, 4-lane gather, 16-bit-tag cache); this file now serves the device
+// builder (builder.cu: BeamRegs + beam_search with ef = ef_construction) and holds the types both share (GraphView, ...).
 //
 // One warp runs one nsw::search (src/index/nsw.rs:133-184).  The pieces:
 //
@@ -180,7 +182,7 @@ struct BeamRegs {
     k2 = __shfl_sync(kFullMask, bm_key(c2), __ffs(m2) - 1);
   }
 
-  __device__ __forceinline__ void sort_prefix(uint32_t) {}  // already sorted (interface shared with BeamHeap)
+  __device__ __forceinline__ void sort_prefix(uint32_t) {}  // already sorted
   __device__ __forceinline__ uint32_t sorted_index(int r) const { return (threadIdx.x & 31) * R + r; }
 
   // w.push(v); if |w| > ef: w.pop_max()  (nsw.rs:171-176).  Precondition: v not in w, and (size < ef or v < maxv).
@@ -207,140 +209,6 @@ struct BeamRegs {
     if (full) ev = maxv; else ++size;
     maxv = at(size - 1);
     return ev;
-  }
-};
-
-// The same abstract beam (w + the unexpanded members of cands) as BeamRegs, kept UNSORTED: slot i = register i / 32 of
-// lane i % 32, slots [0, size) occupied.  The reference only ever asks its two heaps for the minimum unexpanded
-// element, the maximum, membership and "replace the maximum" (nsw.rs:148-176), and each of those is a two-step
-// 32-bit warp reduction (REDUX) over the packed elements instead of a shifted sorted array: an accept costs about
-// half the instructions.  sort_prefix(n) rebuilds BeamRegs' sorted layout for the n smallest when a search is over.
-template <int R>
-struct BeamHeap {
-  uint64_t w[R];
-  uint64_t maxv;     // w.peek_max(), maintained while size >= ef (uniform across the warp)
-  uint32_t size;     // |w|
-  uint32_t spill_n;  // boundary-tie stack depth
-  uint32_t spill_d;  // distance shared by the stack entries
-
-  static __device__ __forceinline__ uint32_t hi32(uint64_t v) { return (uint32_t)(v >> 32); }
-  static __device__ __forceinline__ uint32_t lo32(uint64_t v) { return (uint32_t)v; }
-
-  __device__ __forceinline__ void reset(uint64_t first) {
-    const uint32_t lane = threadIdx.x & 31;
-#pragma unroll
-    for (int r = 0; r < R; ++r) w[r] = kBeamInf;
-    if (lane == 0) w[0] = first;
-    maxv = first;
-    size = 1;
-    spill_n = 0;
-    spill_d = 0;
-  }
-  __device__ __forceinline__ uint32_t F() const { return bm_dist(maxv); }
-
-  __device__ __forceinline__ void refresh_max() {
-    uint64_t m = 0;
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const uint64_t x = (w[r] == kBeamInf) ? 0ull : w[r];
-      m = x > m ? x : m;
-    }
-    const uint32_t mh = __reduce_max_sync(kFullMask, hi32(m));
-    const uint32_t ml = __reduce_max_sync(kFullMask, hi32(m) == mh ? lo32(m) : 0u);
-    maxv = ((uint64_t)mh << 32) | ml;
-  }
-
-  __device__ __forceinline__ bool contains(uint64_t v) const {
-    bool hit = false;
-#pragma unroll
-    for (int r = 0; r < R; ++r) hit |= ((w[r] ^ v) >> 1) == 0;
-    return __any_sync(kFullMask, hit);
-  }
-
-  // cands.pop_min() restricted to members of w: smallest element not yet expanded; marks it expanded.
-  __device__ __forceinline__ bool pop_unexpanded(uint32_t& key) {
-    uint64_t cv = kBeamInf;
-#pragma unroll
-    for (int r = 0; r < R; ++r)
-      if (!(w[r] & 1ull) && w[r] < cv) cv = w[r];
-    const uint32_t mh = __reduce_min_sync(kFullMask, hi32(cv));
-    if (mh == 0xFFFFFFFFu) return false;  // a real element's high word is (distance << 1 | key >> 31) <= 2049
-    const uint32_t ml = __reduce_min_sync(kFullMask, hi32(cv) == mh ? lo32(cv) : 0xFFFFFFFFu);
-    const uint64_t c = ((uint64_t)mh << 32) | ml;
-#pragma unroll
-    for (int r = 0; r < R; ++r)
-      if (w[r] == c) w[r] = c | 1ull;
-    if (maxv == c) maxv = c | 1ull;
-    key = bm_key(c);
-    return true;
-  }
-  // the element pop_unexpanded() would return next if nothing were inserted in between (prefetch prediction; k2 unused)
-  __device__ __forceinline__ void peek_unexpanded2(uint32_t& k1, uint32_t& k2) const {
-    uint64_t cv = kBeamInf;
-#pragma unroll
-    for (int r = 0; r < R; ++r)
-      if (!(w[r] & 1ull) && w[r] < cv) cv = w[r];
-    const uint32_t mh = __reduce_min_sync(kFullMask, hi32(cv));
-    const uint32_t ml = __reduce_min_sync(kFullMask, hi32(cv) == mh ? lo32(cv) : 0xFFFFFFFFu);
-    k1 = (mh == 0xFFFFFFFFu) ? kNoKey : bm_key(((uint64_t)mh << 32) | ml);
-    k2 = kNoKey;
-  }
-
-  // w.push(v); if |w| > ef: w.pop_max()  (nsw.rs:171-176).  Precondition: v not in w, and (size < ef or v < maxv).
-  // Returns the evicted element (kBeamInf when nothing was evicted).
-  __device__ __forceinline__ uint64_t insert(uint64_t v, uint32_t ef) {
-    const uint32_t lane = threadIdx.x & 31;
-    uint64_t ev = kBeamInf;
-    if (size >= ef) {
-      ev = maxv;
-#pragma unroll
-      for (int r = 0; r < R; ++r)
-        if (w[r] == ev) w[r] = v;
-      refresh_max();
-    } else {
-#pragma unroll
-      for (int r = 0; r < R; ++r)
-        if ((size >> 5) == (uint32_t)r && (size & 31u) == lane) w[r] = v;
-      ++size;
-      if (size >= ef) refresh_max();
-    }
-    return ev;
-  }
-
-  // the n smallest elements, ascending: element j moves to register j / 32 of lane j % 32; the rest is dropped
-  __device__ __forceinline__ void sort_prefix(uint32_t n) {
-    const uint32_t lane = threadIdx.x & 31;
-    uint64_t out[R];
-    n = min(n, size);
-#pragma unroll
-    for (int ro = 0; ro < R; ++ro) {
-      out[ro] = kBeamInf;
-      for (uint32_t j = 32u * ro; j < min(n, 32u * ro + 32u); ++j) {
-        uint64_t cv = w[0];
-#pragma unroll
-        for (int r = 1; r < R; ++r) cv = w[r] < cv ? w[r] : cv;
-        const uint32_t mh = __reduce_min_sync(kFullMask, hi32(cv));
-        const uint32_t ml = __reduce_min_sync(kFullMask, hi32(cv) == mh ? lo32(cv) : 0xFFFFFFFFu);
-        const uint64_t c = ((uint64_t)mh << 32) | ml;
-#pragma unroll
-        for (int r = 0; r < R; ++r)
-          if (w[r] == c) w[r] = kBeamInf;
-        if ((j & 31u) == lane) out[ro] = c;
-      }
-    }
-#pragma unroll
-    for (int r = 0; r < R; ++r) w[r] = out[r];
-  }
-  // rank (after sort_prefix) of this lane's register r
-  __device__ __forceinline__ uint32_t sorted_index(int r) const { return 32u * r + (threadIdx.x & 31); }
-  // element of rank i (after sort_prefix), broadcast to every lane
-  __device__ __forceinline__ uint64_t at(uint32_t i) const {
-    const uint32_t r = i >> 5;
-    uint64_t t = w[0];
-#pragma unroll
-    for (int j = 1; j < R; ++j)
-      if (r == (uint32_t)j) t = w[j];
-    return __shfl_sync(kFullMask, t, i & 31u);
   }
 };
 

@@ -1,11 +1,11 @@
 #!/bin/bash
-# Round-2 GPU session f: full -m gpu suite, speculation variants (row ahead / sketch prefetch / tail only), latency.
+# Round-2 GPU session r: tail-gated row-ahead, 10 CTAs/SM; builder tests after the beam.cuh cleanup.
 out=gpurun_out; mkdir -p $out
-L=$out/r02f_ab.log; : > $L
-timeout 1500 python -m pytest tests -q -m gpu > $out/r02f_pytest_gpu.log 2>&1; echo "pytest gpu rc=$?" >> $L; tail -8 $out/r02f_pytest_gpu.log >> $L
+L=$out/r02r_ab.log; : > $L
+timeout 600 python -m pytest tests/test_gpu_builder.py -q -m gpu > $out/r02r_pytest_builder.log 2>&1; echo "pytest builder rc=$?" >> $L; tail -2 $out/r02r_pytest_builder.log >> $L
 python tools/ab.py prepare 10000000 10000 >> $L 2>&1
-for v in cpF s1 s2 s3 s3b s2b s3A; do HB_LIB_PATH=$PWD/variants/$v.so python tools/ab.py run $v 64 2>&1 | tail -1 >> $L; done
-for v in s3 s2; do HB_LIB_PATH=$PWD/variants/$v.so python tools/ab.py run ${v}_sat 64 10 2>&1 | tail -1 >> $L; done
-for ef in 16 128 256; do for v in cpF s3; do HB_LIB_PATH=$PWD/variants/$v.so python tools/ab.py run $v $ef 2>&1 | tail -1 >> $L; done; done
-HB_LIB_PATH=$PWD/variants/s3time.so python tools/ab_time.py 64 2>&1 | tail -8 >> $L
+for v in base tra mb10 tra10 base tra; do HB_LIB_PATH=$PWD/variants/$v.so python tools/ab.py run $v 64 2>&1 | tail -1 >> $L; done
+for v in base tra; do HB_LIB_PATH=$PWD/variants/$v.so python tools/ab.py run ${v}_sat 64 10 2>&1 | tail -1 >> $L; done
+for ef in 16 128 256; do for v in base tra; do HB_LIB_PATH=$PWD/variants/$v.so python tools/ab.py run $v $ef 2>&1 | tail -1 >> $L; done; done
+for v in base tra; do HB_LIB_PATH=$PWD/variants/$v.so python tools/ab.py run ${v}_2500 64 -2500 2>&1 | tail -1 >> $L; done
 cat $L
