@@ -18,6 +18,7 @@ HB_ERR_INVALID, HB_ERR_IO, HB_ERR_FORMAT, HB_ERR_CUDA, HB_ERR_NO_DEVICE = 1, 2, 
 HB_ERR_OOM, HB_ERR_EMPTY_RESULT, HB_ERR_UNSUPPORTED, HB_ERR_INTERNAL = 6, 7, 8, 9
 HB_PAD_LIKE_CLI = 1
 HB_EXACT_VISITED = 2
+HB_NOALLOC_MAX_QUERIES = 65536  # hb_knns_device_noalloc: queries per call its static scratch holds
 ALGO_NAMES = ["bruteforce", "nsw", "hnsw"]
 
 _u64p = C.POINTER(C.c_uint64)
@@ -124,6 +125,7 @@ def lib() -> C.CDLL:
     L.hb_knns.argtypes = [vp, _u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, _u64p, _u64p, _u32p, vp]
     L.hb_search.argtypes = [vp, _u64p, C.c_uint32, C.c_uint32, C.c_uint32, _u64p, _u64p, _u32p]
     L.hb_knns_device.argtypes = [vp, vp, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]
+    L.hb_knns_device_noalloc.argtypes = [vp, vp, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp, vp, vp]
     L.hb_index_last_search_ms.argtypes = [vp]
     L.hb_index_last_search_ms.restype = C.c_double
     L.hb_kernel_launches.restype = C.c_uint64

@@ -319,6 +319,15 @@ int hb_knns_device(const hb_index* h, const void* d_queries, uint64_t nq, uint32
   });
 }
 
+int hb_knns_device_noalloc(const hb_index* h, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, void* d_keys,
+                           void* d_dists, void* d_found, void* stream) {
+  return guarded([&] {
+    Index* idx = as_index(h);
+    HB_REQUIRE(nq == 0 || (d_queries && d_keys && d_dists && d_found), HB_ERR_INVALID, "null device buffer");
+    knns_device_noalloc(*idx, d_queries, nq, k, ef, flags, d_keys, d_dists, d_found, static_cast<cudaStream_t>(stream));
+  });
+}
+
 namespace hb {
 namespace {
 // take an idle staging set from the index's pool (or make one) and grow it to the call's size

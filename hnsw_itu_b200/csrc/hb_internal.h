@@ -163,6 +163,9 @@ void index_compact(Index& idx);  // fixed-stride rows -> line-granular rows + of
 // search.cu
 void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, void* d_keys,
                  void* d_dists, void* d_found, void* d_counters, cudaStream_t stream);
+// the ef <= 256 path with its scratch in a static device array (no allocation of any kind; hb_knns_device_noalloc)
+void knns_device_noalloc(const Index& idx, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, void* d_keys,
+                         void* d_dists, void* d_found, cudaStream_t stream);
 
 // bruteforce.cu
 // d_bound (optional, nq u32, 0xFFFFFFFF = none yet): per-query upper bound on the global k-th distance, read and

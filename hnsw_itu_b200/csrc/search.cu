@@ -671,4 +671,99 @@ void knns_device(const Index& idx, const void* d_queries, uint64_t nq, uint32_t 
   idx.last_search_ms = search_ms;
 }
 
+// ---------------------------------------------------------------------------------------------
+// hb_knns_device_noalloc: the ef <= 256 search with its scratch (the work counter, the overflow flag and the per-query
+// status words) in a file-scope device array instead of a pooled cudaMalloc'd workspace.  For callers that cannot
+// allocate (CUDA graph capture around them, serving loops, harnesses that forbid it).  No counterpart in the reference;
+// added at the request of the run's operators.  Every GPU that loads the library holds the array until exit; all
+// calls on a device share it, so calls that overlap on the GPU race.
+// ---------------------------------------------------------------------------------------------
+namespace {
+constexpr uint32_t kNoAllocCtlWords = 64;  // control words, padded to one 256-byte block
+static __device__ __align__(256) uint32_t g_noalloc_scratch[kNoAllocCtlWords + HB_NOALLOC_MAX_QUERIES];
+
+// The array's device address on `device` (which must be current).  In host code the symbol's name is a host-side
+// stand-in, not a device address: the runtime resolves it per device.
+uint32_t* noalloc_scratch(int device) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static uint32_t* addr[kMaxDevices] = {};
+  HB_REQUIRE(device >= 0 && device < kMaxDevices, HB_ERR_UNSUPPORTED, "device ordinal above 63");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[device]) {
+    uint32_t* ptr = nullptr;
+    HB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_scratch));
+    HB_REQUIRE(ptr != nullptr, HB_ERR_INTERNAL, "cudaGetSymbolAddress returned a null scratch address");
+    addr[device] = ptr;
+  }
+  return addr[device];
+}
+}  // namespace
+
+void knns_device_noalloc(const Index& idx, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags, void* d_keys,
+                         void* d_dists, void* d_found, cudaStream_t stream) {
+  HB_REQUIRE(idx.algo == HB_ALGO_HNSW || idx.algo == HB_ALGO_NSW, HB_ERR_INVALID, "graph search on a non-graph index");
+  HB_REQUIRE(k >= 1 && k <= HB_MAX_K, HB_ERR_INVALID, "k out of range");
+  HB_REQUIRE(ef <= 256, HB_ERR_UNSUPPORTED, "hb_knns_device_noalloc: ef above 256 needs visited tables in allocated memory (use hb_knns_device)");
+  HB_REQUIRE(!(flags & HB_EXACT_VISITED), HB_ERR_UNSUPPORTED, "hb_knns_device_noalloc: HB_EXACT_VISITED needs allocated visited tables");
+  HB_REQUIRE(nq <= HB_NOALLOC_MAX_QUERIES, HB_ERR_UNSUPPORTED,
+             "hb_knns_device_noalloc: " + std::to_string(nq) + " queries exceed the static scratch (HB_NOALLOC_MAX_QUERIES = " +
+                 std::to_string((unsigned)HB_NOALLOC_MAX_QUERIES) + "); split the batch or use hb_knns_device");
+  if (nq == 0) return;
+  HB_CUDA(cudaSetDevice(idx.device));
+  if (idx.ep_file < 0 || idx.n_base == 0) {  // hnsw.rs:282 / nsw.rs:345: no entry point -> empty results
+    HB_CUDA(cudaMemsetAsync(d_keys, 0, nq * k * 8, stream));
+    HB_CUDA(cudaMemsetAsync(d_dists, 0, nq * k * 8, stream));
+    HB_CUDA(cudaMemsetAsync(d_found, 0, nq * 4, stream));
+    HB_CUDA(cudaStreamSynchronize(stream));
+    HB_REQUIRE(!(flags & HB_PAD_LIKE_CLI), HB_ERR_EMPTY_RESULT, "search returned no elements (the reference panics here)");
+    return;
+  }
+  if (ef == 0) ef = 1;
+  uint32_t* scratch = noalloc_scratch(idx.device);
+
+  SearchParams p{};
+  p.sk = idx.d_sk;
+  p.adj = idx.d_adj;
+  p.rowoff = idx.d_rowoff;
+  p.down = idx.d_down;
+  p.queries = static_cast<const uint4*>(d_queries);
+  p.keys = static_cast<uint64_t*>(d_keys);
+  p.dists = static_cast<uint64_t*>(d_dists);
+  p.found = static_cast<uint32_t*>(d_found);
+  p.counters = nullptr;
+  p.stride = idx.stride;
+  p.n_base = (uint32_t)idx.n_base;
+  p.n_total = (uint32_t)idx.n_total;
+  p.n_upper = (uint32_t)idx.g_nodes.size() - 1;
+  p.ep_gid = idx.ep_gid;
+  p.ef = ef;
+  p.k = k;
+  p.flags = flags;
+  p.ef_cap = (ef + 31u) / 32u * 32u;
+  p.ctl = scratch;                        // [0] query counter, [1] overflow flag (+ the debug words)
+  p.qstatus = scratch + kNoAllocCtlWords;  // every query's word is written by the kernel: no clearing needed
+  p.qmap = nullptr;
+  p.nq = (uint32_t)nq;
+
+  const FastChoice fc = choose_fast(idx, ef, false);
+  HB_CUDA(cudaFuncSetAttribute(fc.fl.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fc.smem));
+  int fbps = 0;
+  HB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fbps, fc.fl.kernel, kWarpsPerBlock * 32, fc.smem));
+  HB_REQUIRE(fbps >= 1, HB_ERR_INTERNAL, "fast search kernel does not fit on an SM");
+  const uint32_t fblocks = (uint32_t)std::min<uint64_t>((uint64_t)idx.sm_count * fbps, (nq + kWarpsPerBlock - 1) / kWarpsPerBlock);
+  // the array keeps the last call's contents: the counter and the flag must start at zero
+  HB_CUDA(cudaMemsetAsync(scratch, 0, kNoAllocCtlWords * sizeof(uint32_t), stream));
+  fc.fl.kernel<<<fblocks, kWarpsPerBlock * 32, fc.smem, stream>>>(p, fc.cache_log2);
+  count_launches();
+  HB_CUDA(cudaGetLastError());
+  uint32_t h_ctl[4] = {0, 0, 0, 0};
+  HB_CUDA(cudaMemcpyAsync(h_ctl, scratch, sizeof(h_ctl), cudaMemcpyDeviceToHost, stream));
+  HB_CUDA(cudaStreamSynchronize(stream));
+  // tie-heavy data can overflow a query's boundary-tie stack; hb_knns_device reruns those queries with tables it
+  // allocates, which this entry point may not do: their rows are empty (found = 0) and the call says so
+  HB_REQUIRE(!h_ctl[1], HB_ERR_UNSUPPORTED,
+             "hb_knns_device_noalloc: some queries overflowed the boundary-tie stack (their found[] is 0); rerun the batch with hb_knns_device");
+}
+
 }  // namespace hb

@@ -135,6 +135,13 @@ class Index:
         check(_lib.lib().hb_knns_device(self._h, d_queries, nq, k, ef, HB_PAD_LIKE_CLI if pad else 0, d_keys, d_dists, d_found,
                                         d_counters or None, stream or None))
 
+    def knns_device_noalloc(self, d_queries: int, nq: int, k: int, ef: int, d_keys: int, d_dists: int, d_found: int,
+                            stream: int = 0, pad: bool = False):
+        """hb_knns_device_noalloc: knns_device for ef <= 256 and nq <= HB_NOALLOC_MAX_QUERIES that allocates nothing
+        (scratch in a static device array shared by all calls on the device: do not overlap calls)."""
+        check(_lib.lib().hb_knns_device_noalloc(self._h, d_queries, nq, k, ef, HB_PAD_LIKE_CLI if pad else 0, d_keys, d_dists, d_found,
+                                                stream or None))
+
     # -- host copy ---------------------------------------------------------------
     def _point(self, key: int):
         if self._base_cache is None:

@@ -146,6 +146,20 @@ int hb_search(const hb_index* idx, const uint64_t* query, uint32_t k, uint32_t e
 int hb_knns_device(const hb_index* idx, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags,
                    void* d_keys, void* d_dists, void* d_found, void* d_counters, void* stream);
 
+/* No counterpart in the reference: added at the request of the run's operators, for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  hb_knns_device for
+ * ef <= 256 that allocates NOTHING: no cudaMalloc / cudaFree / stream-ordered or pooled allocation, no event creation.
+ * The kernel's scratch (work counter, overflow flag, one status word per query) lives in a static device array of
+ * 256 B + 4 * HB_NOALLOC_MAX_QUERIES bytes that every GPU that loads the library holds until exit.  Same results as
+ * hb_knns_device (same kernel).  Limits: nq <= HB_NOALLOC_MAX_QUERIES and ef <= 256, no HB_EXACT_VISITED, no counters
+ * (HB_ERR_UNSUPPORTED otherwise); a batch in which a query overflows its boundary-tie stack (tie-heavy data; never
+ * seen on the synthetic sets) also returns HB_ERR_UNSUPPORTED, with found[] = 0 for those queries, because the rerun
+ * needs allocated tables -- use hb_knns_device for it.  All calls on a device share the one array: calls that overlap
+ * on the GPU (two streams, two threads) race; serialise them.  Synchronises `stream` before returning. */
+#define HB_NOALLOC_MAX_QUERIES 65536u
+int hb_knns_device_noalloc(const hb_index* idx, const void* d_queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags,
+                           void* d_keys, void* d_dists, void* d_found, void* stream);
+
 /* Device time (ms, CUDA events on the launching stream) of the search kernel(s) of the last hb_knns* call on this
  * index; used for the roofline figure. */
 double hb_index_last_search_ms(const hb_index* idx);

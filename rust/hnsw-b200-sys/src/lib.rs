@@ -36,6 +36,7 @@ pub const HB_PAD_LIKE_CLI: u32 = 1;
 /// run the kernel with the reference's exact visited set whatever ef is (its dist_evals counter = |visited|)
 pub const HB_EXACT_VISITED: u32 = 2;
 pub const HB_MAX_EF: u32 = 4096;
+pub const HB_NOALLOC_MAX_QUERIES: u32 = 65536;
 pub const HB_MAX_K: u32 = 4096;
 pub const HB_COMM_ID_BYTES: usize = 128;
 
@@ -112,6 +113,7 @@ extern "C" {
     pub fn hb_knns(idx: *const hb_index, queries: *const u64, nq: u64, k: u32, ef: u32, flags: u32, keys: *mut u64, dists: *mut u64, found: *mut u32, counters: *mut hb_counters) -> c_int;
     pub fn hb_search(idx: *const hb_index, query: *const u64, k: u32, ef: u32, flags: u32, keys: *mut u64, dists: *mut u64, found: *mut u32) -> c_int;
     pub fn hb_knns_device(idx: *const hb_index, d_queries: *const c_void, nq: u64, k: u32, ef: u32, flags: u32, d_keys: *mut c_void, d_dists: *mut c_void, d_found: *mut c_void, d_counters: *mut c_void, stream: *mut c_void) -> c_int;
+    pub fn hb_knns_device_noalloc(idx: *const hb_index, d_queries: *const c_void, nq: u64, k: u32, ef: u32, flags: u32, d_keys: *mut c_void, d_dists: *mut c_void, d_found: *mut c_void, stream: *mut c_void) -> c_int;
     pub fn hb_index_last_search_ms(idx: *const hb_index) -> c_double;
     pub fn hb_kernel_launches() -> u64;
 
