@@ -21,13 +21,30 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 // Bounded spin: a protocol bug traps (the launch fails with an error) instead of hanging the GPU.
 // SUSPEND_NS > 0: try_wait carries a suspend-time hint (the warp sleeps in the barrier unit instead of spinning) and
 // the clock is sampled every 16 spins; 0: plain try_wait, clock every 1024 spins.
-template <uint32_t SUSPEND_NS>
+// CLUSTER: acquire at cluster scope (the arrivals come from the peer CTA of a pair as well).
+template <uint32_t SUSPEND_NS, bool CLUSTER = false>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
   long long t0 = 0;
   constexpr uint32_t kEvery = SUSPEND_NS ? 15u : 1023u;
   for (uint32_t spins = 0; !done; ++spins) {
-    if (SUSPEND_NS) {
+    if (SUSPEND_NS && CLUSTER) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(bar), "r"(parity), "r"(SUSPEND_NS)
+          : "memory");
+    } else if (CLUSTER) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(bar), "r"(parity)
+          : "memory");
+    } else if (SUSPEND_NS) {
       asm volatile(
           "{\n\t.reg .pred p;\n\t"
           "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
@@ -88,6 +105,41 @@ __device__ __forceinline__ uint32_t elect_one_sync() {
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// ---- CTA pairs (cta_group::2): two CTAs of a cluster on one TPC issue one MMA over both SMs ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// the shared::cluster address of `addr` (a shared::cta address of this CTA) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+// arrive on a barrier anywhere in the cluster; release at cluster scope (what this thread wrote is visible to the waiter)
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {  // every thread of every CTA of the cluster
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// tcgen05.mma.cta_group::2.kind::mxf4.block_scale: M = 256 over the pair (each CTA's A rows and accumulator lanes are
+// its own 128), B's N rows split in halves between the two CTAs' shared memory at the same offsets.  Leader CTA only.
+__device__ __forceinline__ void umma_mxf4_pair(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t tmem_sf, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%5], p;\n\t}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(tmem_sf)
+      : "memory");
+}
+// the pair's commit: arrives on the barrier at this offset in both CTAs
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"((uint16_t)3)
+               : "memory");
 }
 
 #define HB_TMEM_LD32(v, taddr)                                                                                          \

@@ -15,16 +15,28 @@
 // data tile into a raw buffer: no thread waits on a global load).  Shared memory: query tile 64 KB + 4 stages x 30 KB
 // + raw tile 30 KB.  TMEM: two 128 x 240 fp32 accumulators + the scale columns = 512 columns.  Lists, compaction and
 // the exact merge follow gt_tcgen05.cu; DESIGN.md 4.3 has the measurements behind each of these choices.
+// That is plan 0.  Two more plans of the same kernel (Plan<> below, HB_GT_PLAN) are exact and measured slower: CTA pairs
+// issuing tcgen05.mma.cta_group::2, and four 120-row accumulators.
 #include <cuda.h>  // CUtensorMap and the encode entry point's signature (no libcuda link: resolved through the runtime)
 
 #include <algorithm>
 #include <climits>
+#include <cstdlib>
 
 #include "gt_common.cuh"
 #include "hb_internal.h"
 
 #ifndef HB_GT_PROBE_MMAS
 #define HB_GT_PROBE_MMAS 4
+#endif
+#ifndef HB_GT_PLAN_DEFAULT
+#define HB_GT_PLAN_DEFAULT 0  // kernel plan unless HB_GT_PLAN is set (Plan<> below)
+#endif
+#ifndef HB_GT_MERGE_FENCE
+#define HB_GT_MERGE_FENCE 1  // 120-row plans: one proxy fence per expansion warp and tile instead of one per stage
+#endif
+#ifndef HB_GT_BOUND_AHEAD
+#define HB_GT_BOUND_AHEAD 1
 #endif
 #ifndef HB_GT_SUSPEND_NS
 #define HB_GT_SUSPEND_NS 20000u  // upper bound of one mbarrier.try_wait suspension
@@ -34,32 +46,55 @@ namespace hb {
 namespace {
 
 constexpr int kTileM = 128;   // queries per work item (UMMA M)
-constexpr int kTileN = 240;   // data rows per accumulator tile (UMMA N): 2 x 240 + 16 scale-factor columns <= 512
-constexpr int kGroup = 48;      // accumulator columns an epilogue thread reads per step (240 = 5 x 48)
-constexpr uint32_t kAccStride = 256, kSfCol = 496;  // TMEM columns: accumulators at 0 and 256, scale factors at 496..511
+constexpr int kTileN = 240;   // largest accumulator tile (UMMA N): 2 x 240 + 16 scale-factor columns <= 512
+constexpr uint32_t kSfCol = 496;  // TMEM columns: accumulators from 0 (Plan<>), scale factors at 496..511
 constexpr int kKBlocks = 4;   // 1024 bits = 4 K-blocks of 256 E2M1 (one 128-B swizzle atom row each)
-constexpr int kStages = 4;
 constexpr int kEpiWarps = 4, kExpWarps = 8;
 constexpr int kThreads = (kEpiWarps + kExpWarps + 2) * 32;  // + the MMA warp + the loader warp
 constexpr uint32_t kABytes = kTileM * 512;            // 4 K-blocks x (128 rows x 128 B)
 constexpr uint32_t kAKBlockBytes = kTileM * 128;
-constexpr uint32_t kStageBytes = kTileN * 128;
 // the packed rows of one data tile as ONE tensor-map TMA copy delivers them: 128 B per row, 128-byte swizzle (the
 // 16-byte piece c of row r sits at piece c ^ (r & 7)), so the same piece of eight consecutive rows lies in eight
 // different bank groups.  (One 128-byte bulk copy per row at a padded pitch costs ~54 cycles per copy, 13 k cycles per
 // tile; four large unswizzled copies need lane-rotated reads and selects to dodge the conflicts: 34.4 ms.)
-constexpr uint32_t kRawPitch = 128, kRawBytes = kTileN * kRawPitch;
-constexpr uint32_t kRawOffset = kABytes + kStages * kStageBytes;
-constexpr uint32_t kBarOffset = kRawOffset + kRawBytes;
-static_assert(kStageBytes % 1024 == 0 && kRawOffset % 1024 == 0 && kBarOffset % 8 == 0, "smem layout");
-constexpr uint32_t kSmemBytes = kBarOffset + 192 + 1024;  // + barriers + alignment slack
-
-// instruction descriptor (cute::UMMA::InstrDescriptorBlockScaled layout): A = B = E2M1 (MXF4 format 1), both K-major,
-// scale format E8M0, scale-factor ids 0, N = 240, M = 128, K = 64
-constexpr uint32_t kIdesc = (1u << 7) | (1u << 10) | (1u << 23) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+constexpr uint32_t kRawPitch = 128;
+// Kernel plans (HB_GT_PLAN; 0 is the default, the other two were built, are exact, and measured slower -- DESIGN.md 4.3).
+//  0  one CTA, accumulator tiles of 240 rows, two of them in TMEM, a ring of one tile's four stages.
+//  1  CTA pair (cta_group::2, a cluster of two on one TPC): M = 256 (each CTA its own 128 queries, accumulators in its
+//     own TMEM) and each CTA loads and expands only its HALF of every 240-row tile; half-size stages, so the ring
+//     holds two tiles.
+//  2  one CTA, accumulator tiles of 120 rows, FOUR of them in TMEM (the MMA can run three tiles ahead of the
+//     epilogue instead of one), a ring of two tiles.
+template <int PLAN>
+struct Plan {
+  static constexpr bool pair = PLAN == 1;
+  static constexpr uint32_t tile_n = PLAN == 2 ? 120 : kTileN;      // rows per accumulator tile (UMMA N)
+  static constexpr uint32_t n_acc = PLAN == 2 ? 4 : 2;              // accumulators in TMEM
+  static constexpr uint32_t acc_stride = PLAN == 2 ? 120 : 256;     // TMEM columns between them
+  static constexpr uint32_t group = PLAN == 2 ? 40 : 48;            // accumulator columns an epilogue thread reads per step
+  static constexpr uint32_t rows = pair ? tile_n / 2 : tile_n;      // data rows this CTA expands per tile
+  static constexpr uint32_t rows_per_thread = rows > 128 ? 2 : 1;   // of an expansion group's 128 threads
+  static constexpr uint32_t ring_tiles = rows > 128 ? 1 : 2;        // tiles the stage ring holds
+  static constexpr uint32_t stages = 4 * ring_tiles;
+  static constexpr uint32_t stage_bytes = rows * 128;
+  static constexpr uint32_t raw_bytes = rows * kRawPitch;
+  static constexpr uint32_t raw_off = kABytes + stages * stage_bytes;
+  static constexpr uint32_t bar_off = raw_off + raw_bytes;
+  // barriers: full[stages] empty[stages] tfull[n_acc] tempty[n_acc] a_full a_free raw_full raw_free, then the TMEM base slot
+  static constexpr uint32_t bar_bytes = 16 * stages + 16 * n_acc + 32;
+  static constexpr uint32_t smem_bytes = bar_off + bar_bytes + 16 + 1024;  // + alignment slack
+  // instruction descriptor (cute::UMMA::InstrDescriptorBlockScaled layout): A = B = E2M1 (MXF4 format 1), both K-major,
+  // scale format E8M0, scale-factor ids 0, N = tile_n, M = 128 (256 over a pair), K = 64
+  static constexpr uint32_t idesc = (1u << 7) | (1u << 10) | (1u << 23) | ((tile_n >> 3) << 17) | ((((pair ? 2u : 1u) * kTileM) >> 4) << 24);
+  static_assert(stage_bytes % 1024 == 0 && raw_off % 1024 == 0 && bar_off % 8 == 0, "smem layout");
+  static_assert(smem_bytes <= 227 * 1024, "shared memory");
+  static_assert((n_acc - 1) * acc_stride + tile_n <= kSfCol && tile_n <= acc_stride && tile_n % group == 0 && group > 32 && group <= 48 && group % 8 == 0,
+                "TMEM plan");
+};
 
 using namespace gt;  // mbarrier / tcgen05 helpers, HB_TMEM_LD32 (gt_common.cuh)
 constexpr auto mbar_wait = gt::mbar_wait<HB_GT_SUSPEND_NS>;
+constexpr auto mbar_wait_cluster = gt::mbar_wait<HB_GT_SUSPEND_NS, true>;
 
 #ifdef HB_GT_DIAG
 // per-CTA phase clocks (diagnostic build only, tools/gt_diag.py): [0] kernel cycles, [1] MMA warp waiting for a free
@@ -88,6 +123,12 @@ constexpr uint32_t kTr0 = 3000;
         "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])                        \
       : "r"(taddr)                                                                                                      \
       : "memory")
+
+#define HB_TMEM_LD8(v, taddr)                                                                                           \
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"                          \
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])       \
+               : "r"(taddr)                                                                                           \
+               : "memory")
 
 struct GtParams {
   const uint64_t* data;     // n rows x 16 u64
@@ -213,37 +254,51 @@ __device__ __noinline__ uint64_t gt4_warp_compact_small(uint64_t* buf, uint32_t 
   return ((uint64_t)lo << 32) | woff;
 }
 
-template <bool kRegList>
+template <bool kRegList, int kPlan>
 __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, const __grid_constant__ CUtensorMap tmap) {
+  using PL = Plan<kPlan>;
+  constexpr bool kPair = PL::pair;
+  constexpr uint32_t TN = PL::tile_n, GR = PL::group, NACC = PL::n_acc;
+  constexpr uint32_t kStages = PL::stages, kStageBytes = PL::stage_bytes;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
-  const uint32_t base = (raw + 1023u) & ~1023u;  // swizzle atoms need 1024-B alignment
+  const uint32_t base = (raw + 1023u) & ~1023u;  // swizzle atoms need 1024-B alignment (the same offset in both CTAs of a pair)
   unsigned char* sm = smem_raw + (base - raw);
-  const uint32_t sA = base, sB = base + kABytes, sRaw = base + kRawOffset, sBar = base + kBarOffset;
-  // barriers: full[4] empty[4] tfull[2] tempty[2] a_full a_free raw_full raw_free (112 bytes), then the TMEM base slot
-  const uint32_t bFull = sBar, bEmpty = sBar + 8 * kStages, bTFull = sBar + 16 * kStages, bTEmpty = bTFull + 16, bAFull = bTEmpty + 16,
+  const uint32_t sA = base, sB = base + kABytes, sRaw = base + PL::raw_off, sBar = base + PL::bar_off;
+  const uint32_t bFull = sBar, bEmpty = sBar + 8 * kStages, bTFull = sBar + 16 * kStages, bTEmpty = bTFull + 8 * NACC, bAFull = bTEmpty + 8 * NACC,
                  bAFree = bAFull + 8, bRawFull = bAFree + 8, bRawFree = bRawFull + 8;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + kBarOffset + 128);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + PL::bar_off + PL::bar_bytes);
 
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Pair: the leader (cluster rank 0) issues every MMA, so the barriers its MMA warp waits on -- stage full, accumulator
+  // free, query tile ready -- live in the leader and take the arrivals of BOTH CTAs (remote arrives from the peer); the
+  // barriers the MMA completions signal -- stage empty, accumulator full, query tile free -- exist in both CTAs and the
+  // leader's commit is multicast to both.  The raw-tile barriers are private to each CTA.
+  const uint32_t rank = kPair ? cluster_ctarank() : 0u;
+  constexpr uint32_t kCtas = kPair ? 2u : 1u;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(bFull + 8 * s, kExpWarps / 2);
+    for (uint32_t s = 0; s < kStages; ++s) {
+      mbar_init(bFull + 8 * s, kCtas * (kExpWarps / 2));
       mbar_init(bEmpty + 8 * s, 1);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (uint32_t a = 0; a < NACC; ++a) {
       mbar_init(bTFull + 8 * a, 1);
-      mbar_init(bTEmpty + 8 * a, kEpiWarps * 32);
+      mbar_init(bTEmpty + 8 * a, kPair ? kCtas * kEpiWarps : kEpiWarps * 32);
     }
-    mbar_init(bAFull, kExpWarps);
+    mbar_init(bAFull, kCtas * kExpWarps);
     mbar_init(bAFree, 1);
     mbar_init(bRawFull, 1);
     mbar_init(bRawFree, kExpWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (kPair) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -260,10 +315,18 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
+  if (kPair) cluster_sync_all();  // both CTAs' barriers, TMEM and scale factors are in place before either touches the other
+  else __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
-  const uint32_t n_items = p.n_qtiles * p.n_chunks;
+  // work items: (query tile, chunk of data tiles); a pair takes two adjacent query tiles, one per CTA
+  const uint32_t n_qslots = kPair ? (p.n_qtiles + 1) / 2 : p.n_qtiles;
+  const uint32_t n_items = n_qslots * p.n_chunks;
+  const uint32_t item0 = kPair ? blockIdx.x >> 1 : blockIdx.x, item_step = kPair ? gridDim.x >> 1 : gridDim.x;
+  auto qtile_of = [&](uint32_t item) { return kPair ? (item % n_qslots) * 2 + rank : item % n_qslots; };
+  // the leader's copies of the barriers both CTAs arrive on (shared::cluster addresses; own CTA when not paired)
+  const uint32_t bFullL = kPair ? mapa_u32(bFull, 0) : bFull, bTEmptyL = kPair ? mapa_u32(bTEmpty, 0) : bTEmpty,
+                 bAFullL = kPair ? mapa_u32(bAFull, 0) : bAFull;
 #if defined(HB_GT_PROBE_STS) && HB_GT_PROBE_STS < 8
   for (uint32_t i = threadIdx.x; i < kStages * kStageBytes / 16; i += blockDim.x)
     asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(sB + i * 16), "r"(0u) : "memory");
@@ -276,8 +339,8 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
     const uint32_t row = warp * 32 + lane;
     uint32_t tcount = 0;
     [[maybe_unused]] long long dg_tfull = 0, dg_ins = 0;
-    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
-      const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
+    for (uint32_t item = item0; item < n_items; item += item_step) {
+      const uint32_t qtile = qtile_of(item), chunk = item / n_qslots;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
       const uint32_t q = qtile * kTileM + row;
       const bool live = q < p.nq;
@@ -306,33 +369,44 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
       // other item's keys may be larger).  Rows failing either test cannot be in the global top-k.
       float T = live ? -INFINITY : INFINITY;  // accumulators are exact small integers in fp32: pop(q) - Hamming
       uint32_t* gq = p.gthr + (live ? q : 0);
-      const uint64_t row_end = min(p.n, (uint64_t)t1 * kTileN);
+      const uint64_t row_end = min(p.n, (uint64_t)t1 * TN);
+      // the shared bound is read one tile ahead: when the epilogue is what the kernel waits for, an accumulator is
+      // already full when the loop comes round and the L2 round trip of this load would be paid on every tile
+      [[maybe_unused]] uint32_t g_ahead = *reinterpret_cast<volatile uint32_t*>(gq);
       for (uint32_t t = t0; t < t1; ++t, ++tcount) {
-        const uint32_t acc = tcount & 1, use = tcount >> 1;
+        const uint32_t acc = tcount % NACC, use = tcount / NACC;
+#if HB_GT_BOUND_AHEAD
+        const uint32_t g_now = g_ahead;
+#else
         const uint32_t g_now = *reinterpret_cast<volatile uint32_t*>(gq);
+#endif
         {
           HB_DIAG_T0();
           mbar_wait(bTFull + 8 * acc, use & 1);
           HB_DIAG_ADD(dg_tfull);
         }
+#if HB_GT_BOUND_AHEAD
+        g_ahead = *reinterpret_cast<volatile uint32_t*>(gq);
+#endif
         HB_TRACE(tcount, 2 + warp);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const float Tg = (g_now == 0xFFFFFFFFu) ? -INFINITY : (float)(popq - (int)g_now) - 1.0f;
         float Te = fmaxf(T, Tg);
-        const uint32_t taddr = tmem + ((warp * 32u) << 16) + acc * kAccStride;
-        const uint64_t tile_row0 = (uint64_t)t * kTileN;
+        const uint32_t taddr = tmem + ((warp * 32u) << 16) + acc * PL::acc_stride;
+        const uint64_t tile_row0 = (uint64_t)t * TN;
 #pragma unroll 1
-        for (int g = 0; g < kTileN / kGroup; ++g) {
+        for (int g = 0; g < (int)(TN / GR); ++g) {
           uint32_t h0 = 0, h1 = 0;
           bool hit;
-          float m8[kGroup / 8];  // maxima of the group's six octets of columns
+          float m8[GR / 8];  // maxima of the group's six octets of columns
           {
-            uint32_t v[kGroup];
-            HB_TMEM_LD32(v, taddr + g * kGroup);
-            HB_TMEM_LD16((v + 32), taddr + g * kGroup + 32);
+            uint32_t v[GR];
+            HB_TMEM_LD32(v, taddr + g * GR);
+            if constexpr (GR == 48) HB_TMEM_LD16((v + 32), taddr + g * GR + 32);
+            else HB_TMEM_LD8((v + 32), taddr + g * GR + 32);
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-            for (int j = 0; j < kGroup / 8; ++j) {
+            for (int j = 0; j < GR / 8; ++j) {
               float a = __uint_as_float(v[8 * j]);
 #pragma unroll
               for (int c = 1; c < 8; ++c) a = fmaxf(a, __uint_as_float(v[8 * j + c]));
@@ -340,13 +414,13 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
             }
             float mx = m8[0];
 #pragma unroll
-            for (int j = 1; j < kGroup / 8; ++j) mx = fmaxf(mx, m8[j]);
+            for (int j = 1; j < GR / 8; ++j) mx = fmaxf(mx, m8[j]);
             hit = __any_sync(0xFFFFFFFFu, mx > Te);
             if (kRegList && hit) {  // warp-uniform: which columns pass for which lane
 #pragma unroll
               for (int c = 0; c < 32; ++c) h0 |= (uint32_t)(__uint_as_float(v[c]) > Te) << c;
 #pragma unroll
-              for (int c = 0; c < kGroup - 32; ++c) h1 |= (uint32_t)(__uint_as_float(v[32 + c]) > Te) << c;
+              for (int c = 0; c < GR - 32; ++c) h1 |= (uint32_t)(__uint_as_float(v[32 + c]) > Te) << c;
             }
           }
           if (!kRegList && hit) {
@@ -354,11 +428,11 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
             // (the accumulator is still ours) and append the ones that pass to their own buffers, in parallel and with
             // static register indices.  A buffer that could overflow inside the octet is compacted first.
             HB_DIAG_T0();
-            const uint64_t r0 = tile_row0 + (uint64_t)g * kGroup;
-            const uint32_t nvalid = (uint32_t)min((uint64_t)kGroup, row_end > r0 ? row_end - r0 : 0);
+            const uint64_t r0 = tile_row0 + (uint64_t)g * GR;
+            const uint32_t nvalid = (uint32_t)min((uint64_t)GR, row_end > r0 ? row_end - r0 : 0);
             uint32_t fb = 0;
 #pragma unroll
-            for (int j = 0; j < kGroup / 8; ++j) fb |= (uint32_t)(m8[j] > Te) << j;
+            for (int j = 0; j < GR / 8; ++j) fb |= (uint32_t)(m8[j] > Te) << j;
             uint32_t um = __reduce_or_sync(0xFFFFFFFFu, fb);
             while (um) {
               const uint32_t c0 = 8u * ((uint32_t)__ffs((int)um) - 1u);
@@ -381,7 +455,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
               uint32_t w[8];
               asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                            : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-                           : "r"(taddr + g * kGroup + c0)
+                           : "r"(taddr + g * GR + c0)
                            : "memory");
               asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
@@ -397,16 +471,16 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
             // Rare path, kept warp-uniform: for every column some lane wants, each lane re-reads its own value of that
             // column from TMEM (the accumulator is still ours) and the lanes that pass run one copy of the insert.
             HB_DIAG_T0();
-            const uint64_t r0 = tile_row0 + (uint64_t)g * kGroup;
-            const uint32_t nvalid = (uint32_t)min((uint64_t)kGroup, row_end > r0 ? row_end - r0 : 0);
+            const uint64_t r0 = tile_row0 + (uint64_t)g * GR;
+            const uint32_t nvalid = (uint32_t)min((uint64_t)GR, row_end > r0 ? row_end - r0 : 0);
             uint64_t m = (uint64_t)__reduce_or_sync(0xFFFFFFFFu, h0) | ((uint64_t)__reduce_or_sync(0xFFFFFFFFu, h1) << 32);
-            if (nvalid < (uint32_t)kGroup) m &= (1ull << nvalid) - 1ull;
+            if (nvalid < GR) m &= (1ull << nvalid) - 1ull;
             {
               while (m) {
                 const uint32_t col = (uint32_t)__ffsll((long long)m) - 1u;
                 m &= m - 1;
                 uint32_t xb;
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(xb) : "r"(taddr + g * kGroup + col) : "memory");
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(xb) : "r"(taddr + g * GR + col) : "memory");
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 const float x = __uint_as_float(xb);
                 if (x > Te) {
@@ -451,7 +525,12 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
           }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        mbar_arrive(bTEmpty + 8 * acc);
+        if (kPair) {  // one arrival per warp on the leader's barrier
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(bTEmptyL + 8 * acc);
+        } else {
+          mbar_arrive(bTEmpty + 8 * acc);
+        }
         HB_TRACE(tcount, 6 + warp);
       }
       if (kRegList && live) {
@@ -472,11 +551,11 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
     const uint32_t ew = warp - kEpiWarps;
     const uint32_t et = ew * 32 + lane;  // 0..255: thread of the expansion role (the query-tile fill is indexed by it)
     const uint32_t grp = ew >> 2, wi = ew & 3u;  // a group = one warp on each SM sub-partition (warp id % 4)
-    uint32_t stage = 2 * grp, sphase = 0, it = 0;
+    uint32_t it = 0;
     [[maybe_unused]] long long dg_empty = 0, dg_fence = 0, dg_afree = 0, dg_top = 0, dg_sts = 0;
     uint32_t xt = 0;  // tiles so far: parity of the raw buffer
-    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      const uint32_t qtile = item % p.n_qtiles, chunk = item / p.n_qtiles;
+    for (uint32_t item = item0; item < n_items; item += item_step, ++it) {
+      const uint32_t qtile = qtile_of(item), chunk = item / n_qslots;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
       // ---- A: the query tile.  Word c of a K-block's eight fills 16-byte chunk c; output word u of the chunk holds,
       // in nibble j, the element for bit 4j + u of the word: +-2, +-1, +-0.5, +-0.5 (sign bit = nibble bit 3, set when the
@@ -513,7 +592,10 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
-        if (lane == 0) mbar_arrive(bAFull);
+        if (lane == 0) {
+          if (kPair) mbar_arrive_cluster(bAFullL);
+          else mbar_arrive(bAFull);
+        }
       }
       // ---- B: data tiles ----
       // The loader warp's bulk copies put the tile's packed rows in the raw buffer; each thread takes the 64 bytes its
@@ -523,17 +605,19 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
       // Two groups of four warps fill alternate pairs of stages: group 0 the K-blocks 0,1 of every tile, group 1 the
       // K-blocks 2,3, so one group stores while the other sits in its fence.  Eight consecutive lanes read and write
       // eight consecutive rows: no bank conflicts on either side.
+      // 120-row plans: one row per thread (rows 32 wi + lane) and the ring holds two tiles.
+      constexpr int kRowsPerThread = PL::rows_per_thread;
       for (uint32_t t = t0; t < t1; ++t, ++xt) {
-        uint32_t cur[2][16];
+        uint32_t cur[kRowsPerThread][16];
         {
           HB_DIAG_T0();
           mbar_wait(bRawFull, xt & 1);
           HB_DIAG_ADD(dg_top);
         }
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const uint32_t lrow = 64 * wi + 32 * h + lane;  // lrow & 7 == lane & 7; rows past the data end arrive as zeros
-          const uint32_t ra = sRaw + (lrow < (uint32_t)kTileN ? lrow : 0u) * kRawPitch;
+        for (int h = 0; h < kRowsPerThread; ++h) {
+          const uint32_t lrow = 32 * kRowsPerThread * wi + 32 * h + lane;  // lrow & 7 == lane & 7; rows past the data end arrive as zeros
+          const uint32_t ra = sRaw + (lrow < PL::rows ? lrow : 0u) * kRawPitch;
 #pragma unroll
           for (int e = 0; e < 4; ++e)
             asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
@@ -546,7 +630,7 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
         {
           uint32_t dep = 0;
 #pragma unroll
-          for (int h = 0; h < 2; ++h)
+          for (int h = 0; h < kRowsPerThread; ++h)
 #pragma unroll
             for (int e = 0; e < 16; ++e) dep |= cur[h][e];
           if (dep == 0xFFFFFFFFu && t == 0xFFFFFFFFu) asm volatile("st.shared.b32 [%0], %1;" ::"r"(sRaw), "r"(dep) : "memory");
@@ -554,9 +638,51 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
         // (the copy for the next tile then has this whole tile's expansion time to land)
         __syncwarp();
         if (lane == 0) mbar_arrive(bRawFree);
+        // group g fills K-blocks 2g, 2g + 1 of the tile's four stages; the ring position and its phase follow the tile count
+        const uint32_t sbase = (xt % PL::ring_tiles) * 4, sphase = (xt / PL::ring_tiles) & 1u;
+        if constexpr (kRowsPerThread == 1 && HB_GT_MERGE_FENCE) {
+          // half-size stages: both of the group's K-blocks behind ONE proxy fence (the fence, not the stores, is what an
+          // expansion warp spends its time in), so a row costs as many fences as it does with 240-row stages
+          const uint32_t st0 = sbase + 2 * grp;
+          {
+            HB_DIAG_T0();
+            mbar_wait(bEmpty + 8 * st0, sphase ^ 1);
+            mbar_wait(bEmpty + 8 * (st0 + 1), sphase ^ 1);
+            HB_DIAG_ADD(dg_empty);
+          }
+          const uint32_t lrow = 32 * wi + lane;
+          if (lrow < PL::rows) {
+#pragma unroll
+            for (int sg = 0; sg < 2; ++sg) {
+              const uint32_t rowaddr = sB + (st0 + sg) * kStageBytes + lrow * 128;
+#pragma unroll
+              for (int c = 0; c < 8; ++c) {
+                const uint32_t w = cur[0][8 * sg + c];
+                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + (((uint32_t)c ^ (lane & 7u)) << 4)), "r"(w & 0x11111111u),
+                             "r"(w & 0x22222222u), "r"(w & 0x44444444u), "r"((w >> 1) & 0x44444444u)
+                             : "memory");
+              }
+            }
+          }
+          {
+            HB_DIAG_T0();
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            HB_DIAG_ADD(dg_fence);
+          }
+          if (lane == 0) {
+            if (kPair) {
+              mbar_arrive_cluster(bFullL + 8 * st0);
+              mbar_arrive_cluster(bFullL + 8 * (st0 + 1));
+            } else {
+              mbar_arrive(bFull + 8 * st0);
+              mbar_arrive(bFull + 8 * (st0 + 1));
+            }
+          }
+        } else {
 #pragma unroll
         for (int sg = 0; sg < 2; ++sg) {
-          [[maybe_unused]] const uint32_t kb = 2 * grp + sg;
+          const uint32_t kb = 2 * grp + sg, stage = sbase + kb;
           {
             HB_DIAG_T0();
             mbar_wait(bEmpty + 8 * stage, sphase ^ 1);
@@ -567,10 +693,10 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
 #define HB_GT_PROBE_STS 8  // probe builds (wrong results): fewer stores or fewer MMAs, to time the other side alone
 #endif
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const uint32_t lrow = 64 * wi + 32 * h + lane;
+          for (int h = 0; h < kRowsPerThread; ++h) {
+            const uint32_t lrow = 32 * kRowsPerThread * wi + 32 * h + lane;
             const uint32_t rowaddr = sB + stage * kStageBytes + lrow * 128;
-            if (lrow < (uint32_t)kTileN) {
+            if (lrow < PL::rows) {
 #pragma unroll
               for (int c = 0; c < HB_GT_PROBE_STS; ++c) {  // E2M1 codes 0001 = 0.5, 0010 = 1, 0100 = 2; bit 3 of each nibble reuses 2
                 const uint32_t w = cur[h][8 * sg + c];
@@ -589,12 +715,13 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
             __syncwarp();
             HB_DIAG_ADD(dg_fence);
           }
-          if (lane == 0) mbar_arrive(bFull + 8 * stage);
+          if (lane == 0) {
+            if (kPair) mbar_arrive_cluster(bFullL + 8 * stage);
+            else mbar_arrive(bFull + 8 * stage);
+          }
           if (wi == 0) HB_TRACE(xt, 10 + kb);
-          stage = (stage + 1) & (kStages - 1);
         }
-        stage = (stage + 2) & (kStages - 1);  // the other group's pair; four stages = one tile, so the phase flips per tile
-        sphase ^= 1;
+        }  // (separate fences)
       }
     }
 #ifdef HB_GT_DIAG
@@ -612,24 +739,28 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
     [[maybe_unused]] long long dg_tempty = 0, dg_full = 0;
     [[maybe_unused]] const long long dg_start = clock64();
     const uint64_t da0 = umma_desc(sA), db0 = umma_desc(sB);
-    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      const uint32_t chunk = item / p.n_qtiles;
+    // pair: only the leader issues; the descriptors name the same offsets in both CTAs' shared memory
+    for (uint32_t item = item0; item < n_items && rank == 0; item += item_step, ++it) {
+      const uint32_t chunk = item / n_qslots;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
-      mbar_wait(bAFull, it & 1);
+      if (kPair) mbar_wait_cluster(bAFull, it & 1);
+      else mbar_wait(bAFull, it & 1);
       for (uint32_t t = t0; t < t1; ++t, ++tcount) {
-        const uint32_t acc = tcount & 1, ause = tcount >> 1;
+        const uint32_t acc = tcount % NACC, ause = tcount / NACC;
         {
           HB_DIAG_T0();
-          mbar_wait(bTEmpty + 8 * acc, (ause & 1) ^ 1);
+          if (kPair) mbar_wait_cluster(bTEmpty + 8 * acc, (ause & 1) ^ 1);
+          else mbar_wait(bTEmpty + 8 * acc, (ause & 1) ^ 1);
           HB_DIAG_ADD(dg_tempty);
         }
         HB_TRACE(tcount, 0);
-        const uint32_t tmem_d = tmem + acc * kAccStride;
+        const uint32_t tmem_d = tmem + acc * PL::acc_stride;
 #pragma unroll
         for (int kb = 0; kb < kKBlocks; ++kb) {
           {
             HB_DIAG_T0();
-            mbar_wait(bFull + 8 * stage, sphase);
+            if (kPair) mbar_wait_cluster(bFull + 8 * stage, sphase);
+            else mbar_wait(bFull + 8 * stage, sphase);
             HB_DIAG_ADD(dg_full);
           }
           HB_TRACE(tcount, 18 + kb);
@@ -637,12 +768,22 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
           if (elect_one_sync()) {
             const uint64_t da = da0 + (uint64_t)(kb * (kAKBlockBytes >> 4)), db = db0 + (uint64_t)(stage * (kStageBytes >> 4));
 #pragma unroll
-            for (int j = 0; j < HB_GT_PROBE_MMAS; ++j)  // K = 64 E2M1 per instruction: +32 B inside the swizzle atom = +2 in the encoded address
-              umma_mxf4(tmem_d, da + 2 * j, db + 2 * j, kIdesc, tmem + kSfCol, (kb | j) != 0);
-            umma_commit(bEmpty + 8 * stage);
-            if (kb == kKBlocks - 1) {
-              umma_commit(bTFull + 8 * acc);
-              if (t == t1 - 1) umma_commit(bAFree);
+            for (int j = 0; j < HB_GT_PROBE_MMAS; ++j) {  // K = 64 E2M1 per instruction: +32 B inside the swizzle atom = +2 in the encoded address
+              if (kPair) umma_mxf4_pair(tmem_d, da + 2 * j, db + 2 * j, PL::idesc, tmem + kSfCol, (kb | j) != 0);
+              else umma_mxf4(tmem_d, da + 2 * j, db + 2 * j, PL::idesc, tmem + kSfCol, (kb | j) != 0);
+            }
+            if (kPair) {
+              umma_commit_pair(bEmpty + 8 * stage);
+              if (kb == kKBlocks - 1) {
+                umma_commit_pair(bTFull + 8 * acc);
+                if (t == t1 - 1) umma_commit_pair(bAFree);
+              }
+            } else {
+              umma_commit(bEmpty + 8 * stage);
+              if (kb == kKBlocks - 1) {
+                umma_commit(bTFull + 8 * acc);
+                if (t == t1 - 1) umma_commit(bAFree);
+              }
             }
           }
           __syncwarp();
@@ -654,6 +795,8 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
         }
       }
     }
+    // pair: the last multicast commits have landed in both CTAs before either leaves (the final cluster barrier follows)
+    if (kPair && rank == 0 && it > 0) mbar_wait(bAFree, (it - 1) & 1);
 #ifdef HB_GT_DIAG
     if (lane == 0) {
       g_gt4_diag[blockIdx.x * 16 + 0] = clock64() - dg_start;
@@ -665,15 +808,15 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
     // ===================== loader: the tile's packed rows into the raw buffer, one TMA copy =====================
     // (async proxy end to end: the copies complete on raw_full's transaction count, no thread waits on a load)
     uint32_t xt = 0;
-    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
-      const uint32_t chunk = item / p.n_qtiles;
+    for (uint32_t item = item0; item < n_items; item += item_step) {
+      const uint32_t chunk = item / n_qslots;
       const uint32_t t0 = chunk * p.tiles_per_chunk, t1 = min(p.n_tiles, t0 + p.tiles_per_chunk);
       for (uint32_t t = t0; t < t1; ++t, ++xt) {
         mbar_wait(bRawFree, (xt & 1) ^ 1);
-        if (lane == 0) {
-          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bRawFull), "r"(kRawBytes) : "memory");
+        if (lane == 0) {  // pair: this CTA's half of the tile's rows
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bRawFull), "r"(PL::raw_bytes) : "memory");
           asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(sRaw),
-                       "l"(&tmap), "r"(0), "r"((int)(t * (uint32_t)kTileN)), "r"(bRawFull)
+                       "l"(&tmap), "r"(0), "r"((int)(t * TN + rank * PL::rows)), "r"(bRawFull)
                        : "memory");
         }
         __syncwarp();
@@ -682,10 +825,12 @@ __global__ void __launch_bounds__(kThreads, 1) gt_mxf4_kernel(const GtParams p, 
   }
 
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
+  if (kPair) cluster_sync_all();  // neither CTA's shared memory or TMEM goes away while the other may still signal it
+  else __syncthreads();
   if (warp == 0) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+    if (kPair) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
   }
 }
 
@@ -736,7 +881,16 @@ void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offse
   p.nq = (uint32_t)nq;
   p.k = k;
   p.n_qtiles = (uint32_t)((nq + kTileM - 1) / kTileM);
-  p.n_tiles = (uint32_t)((n + kTileN - 1) / kTileN);
+  const char* plan_str = std::getenv("HB_GT_PLAN");  // read per call: the tests switch plans inside one process
+  const int plan_env = plan_str ? std::atoi(plan_str) : HB_GT_PLAN_DEFAULT;
+  int plan = (plan_env >= 0 && plan_env <= 2) ? plan_env : HB_GT_PLAN_DEFAULT;
+  if (plan == 1 && (sms < 2 || p.n_qtiles < 2)) plan = 0;
+  const bool pair = plan == 1;
+  const uint32_t tile_n = plan == 2 ? Plan<2>::tile_n : Plan<0>::tile_n;
+  p.n_tiles = (uint32_t)((n + tile_n - 1) / tile_n);
+  // CTA pairs: two adjacent query tiles per work item, one per CTA; the pair shares the chunk's data tiles
+  const uint32_t n_qslots = pair ? (p.n_qtiles + 1) / 2 : p.n_qtiles;
+  const uint32_t workers = pair ? (uint32_t)sms / 2 : (uint32_t)sms;
   // chunks of data tiles: enough items to fill the grid several times over, picked so the last wave is nearly full
   uint32_t best_chunks = 1;
   double best_eff = -1.0;
@@ -744,13 +898,13 @@ void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offse
   for (uint32_t c = 1; c <= max_chunks; ++c) {
     const uint32_t tpc = (p.n_tiles + c - 1) / c;
     const uint32_t chunks = (p.n_tiles + tpc - 1) / tpc;
-    const uint64_t items = (uint64_t)chunks * p.n_qtiles;
-    const uint64_t waves = (items + sms - 1) / sms;
+    const uint64_t items = (uint64_t)chunks * n_qslots;
+    const uint64_t waves = (items + workers - 1) / workers;
     // cost model: waves x (tiles per chunk + per-item overhead: writing the query tile and refilling the item's lists,
     // in tile times -- register lists (k <= 16) refill in ~25, lists in global memory in ~4 per entry)
-    const double overhead = 4.0 + (k <= 16 ? 50.0 : 0.5 * k);
+    const double overhead = (4.0 + (k <= 16 ? 50.0 : 0.5 * k)) * (double)Plan<0>::tile_n / tile_n;
     const double cost = (double)waves * (tpc + overhead);
-    const double eff = ((double)p.n_tiles * p.n_qtiles / sms) / cost;
+    const double eff = ((double)p.n_tiles * n_qslots / workers) / cost;
     if (eff > best_eff + 1e-9) {
       best_eff = eff;
       best_chunks = chunks;
@@ -784,7 +938,7 @@ void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offse
       HB_REQUIRE(false, HB_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled is not available from this driver");
     }
     const cuuint64_t gdim[2] = {32, n}, gstride[1] = {128};
-    const cuuint32_t box[2] = {32, (cuuint32_t)kTileN}, estride[2] = {1, 1};
+    const cuuint32_t box[2] = {32, plan == 0 ? Plan<0>::rows : plan == 1 ? Plan<1>::rows : Plan<2>::rows}, estride[2] = {1, 1};
     const CUresult r = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(d_data), gdim, gstride, box, estride,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -793,14 +947,37 @@ void ground_truth_mxf4_device(const void* d_data, uint64_t n, uint64_t key_offse
       HB_REQUIRE(false, HB_ERR_CUDA, "cuTensorMapEncodeTiled failed");
     }
   }
-  const uint32_t n_items = p.n_qtiles * p.n_chunks;
-  const uint32_t grid = std::min<uint32_t>(n_items, (uint32_t)sms);
-  if (k <= 16) {
-    HB_CUDA(cudaFuncSetAttribute(gt_mxf4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    gt_mxf4_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(p, tmap);
+  const uint32_t n_items = n_qslots * p.n_chunks;
+  cudaError_t le = cudaSuccess;
+  auto launch = [&](auto kernel, uint32_t smem, uint32_t cluster) {
+    le = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (le != cudaSuccess) return;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(cluster * std::min<uint32_t>(n_items, workers));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = cluster;
+    attr.val.clusterDim.y = attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = cluster > 1 ? 1 : 0;
+    le = cudaLaunchKernelEx(&cfg, kernel, p, tmap);
+  };
+  if (plan == 1) {
+    if (k <= 16) launch(gt_mxf4_kernel<true, 1>, Plan<1>::smem_bytes, 2);
+    else launch(gt_mxf4_kernel<false, 1>, Plan<1>::smem_bytes, 2);
+  } else if (plan == 2) {
+    if (k <= 16) launch(gt_mxf4_kernel<true, 2>, Plan<2>::smem_bytes, 1);
+    else launch(gt_mxf4_kernel<false, 2>, Plan<2>::smem_bytes, 1);
   } else {
-    HB_CUDA(cudaFuncSetAttribute(gt_mxf4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    gt_mxf4_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(p, tmap);
+    if (k <= 16) launch(gt_mxf4_kernel<true, 0>, Plan<0>::smem_bytes, 1);
+    else launch(gt_mxf4_kernel<false, 0>, Plan<0>::smem_bytes, 1);
+  }
+  if (le != cudaSuccess) {
+    cudaFreeAsync(partial, stream);
+    HB_CUDA(le);
   }
   count_launches();
   cudaError_t e = cudaGetLastError();

@@ -199,6 +199,33 @@ def test_ground_truth_tcgen05_vs_oracle(hb, oracle, dp, n, nq, k, algo):
     assert md[0, 0] == 0 and mk[0, 0] <= n // 2
 
 
+@pytest.mark.parametrize("plan", [1, 2])
+@pytest.mark.parametrize("dp,n,nq,k", [
+    (1024, 20000, 300, 10),   # three query tiles: a full pair and a pair whose second CTA has no queries
+    (16, 9001, 257, 100),     # ties everywhere, k = 100, ragged last data tile, odd number of query tiles
+    (1024, 119, 129, 10),     # less than one 120-row tile
+    (1024, 513, 257, 1024),   # k at the supported maximum
+])
+def test_ground_truth_mxf4_kernel_plans(hb, oracle, monkeypatch, plan, dp, n, nq, k):
+    """The E2M1 kernel's alternative plans (HB_GT_PLAN: 1 = CTA pairs issuing tcgen05.mma.cta_group::2 with each CTA
+    expanding half of every data tile, 2 = four 120-row accumulators) against the default plan and the oracle."""
+    from oracle import oracle as orc
+    p = orc.SynthParams(latent_dim=8, n_clusters=16, distinct_planes=dp)
+    data = oracle.synth(n, 171, p)
+    q = oracle.synth(nq, 172, p)
+    q[0] = data[n // 2]
+    q[-1] = ~data[n - 1]
+    monkeypatch.delenv("HB_GT_PLAN", raising=False)
+    dk, dd = hb.ground_truth(data, q, k, algo="mxf4")
+    monkeypatch.setenv("HB_GT_PLAN", str(plan))
+    mk, md = hb.ground_truth(data, q, k, algo="mxf4")
+    monkeypatch.delenv("HB_GT_PLAN", raising=False)
+    assert np.array_equal(mk, dk) and np.array_equal(md, dd)
+    ok, od = oracle.ground_truth(data, q, k)
+    m = min(n, k)
+    assert np.array_equal(mk[:, :m], ok[:, :m]) and np.array_equal(md[:, :m], od[:, :m])
+
+
 @pytest.mark.parametrize("algo", ["mma", "mxf4"])
 def test_ground_truth_tcgen05_all_bit_positions(hb, algo):
     """Every one of the 1024 bit positions contributes exactly 1 to the distance (the operand scaling/permutation
