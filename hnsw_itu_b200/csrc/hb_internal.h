@@ -119,6 +119,11 @@ struct CallBuffers {
   uint32_t* found = nullptr; // cap_q
   hb_counters* ctr = nullptr;  // cap_q
   uint64_t cap_q = 0, cap_out = 0;
+  // page-locked, mapped host staging for callers with pageable buffers (hb_knns): the kernel reads the queries and
+  // writes the results through these across PCIe, overlapped with the search, like it does for pinned caller memory
+  uint64_t *hq = nullptr, *hkeys = nullptr, *hdists = nullptr;
+  uint32_t* hfound = nullptr;
+  uint64_t hcap_q = 0, hcap_out = 0;
   cudaStream_t stream = nullptr;
 };
 

@@ -110,6 +110,7 @@ Index::~Index() {
   ws_pool.clear();
   for (CallBuffers& b : pool) {
     cudaFree(b.q); cudaFree(b.keys); cudaFree(b.dists); cudaFree(b.found); cudaFree(b.ctr);
+    cudaFreeHost(b.hq); cudaFreeHost(b.hkeys); cudaFreeHost(b.hdists); cudaFreeHost(b.hfound);
     if (b.stream) cudaStreamDestroy(b.stream);
   }
 }

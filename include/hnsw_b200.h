@@ -130,7 +130,9 @@ int hb_index_graph_export(const hb_index* idx, uint32_t graph, uint64_t* sketche
 
 /* Index::knns (src/index/mod.rs:28-42) through Indexes::search
  * (cli/src/main.rs:457-477): one batched launch, results in input order.
- * HOST buffers; H2D/D2H copies happen inside.  keys/dists are (nq, k) u64,
+ * HOST buffers; the transfers happen inside (page-locked caller memory is used in
+ * place; pageable memory goes through page-locked staging owned by the index,
+ * copied by a few helper threads).  keys/dists are (nq, k) u64,
  * found (nq) u32 = results before padding (<= min(k, ef)); rows are
  * zero-filled past found[i] unless HB_PAD_LIKE_CLI.  counters may be NULL. */
 int hb_knns(const hb_index* idx, const uint64_t* queries, uint64_t nq, uint32_t k, uint32_t ef, uint32_t flags,
