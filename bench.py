@@ -630,8 +630,9 @@ def report(R, a, idx, s):
         "cpu_baseline": cpu,
         "e2e": {"value": world * a.nq * a.steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": a.nq * 128,
                 "d2h_bytes_per_step": a.nq * a.k * 16 + a.nq * 4, "ms_per_step": e2e_s / a.steps * 1e3,
-                "how": "hb_knns on PAGEABLE host buffers (a Rust Vec<Sketch> / numpy array): cudaMemcpyAsync of the queries to a pooled "
-                       "staging set, search, cudaMemcpyAsync of keys / distances / found back, all inside the timed region",
+                "how": "hb_knns on PAGEABLE host buffers (a Rust Vec<Sketch> / numpy array): threaded host copy of the queries into the "
+                       "index's page-locked staging, the kernel reading them and writing keys / distances / found across PCIe, threaded "
+                       "copy of the results into the caller's arrays, all inside the timed region (HB_HOST_STAGING=0: cudaMemcpyAsync both ways)",
                 "pinned": {"value": world * a.nq * a.steps / e2e_pin_s, "ms_per_step": e2e_pin_s / a.steps * 1e3,
                            "how": "same call on page-locked buffers: the kernel reads queries from and writes results to mapped host memory in place"}},
         "gpu_launches": int(s["launches"]), "clocks": s["clocks"], "parity": parity,
