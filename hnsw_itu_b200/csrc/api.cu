@@ -330,6 +330,9 @@ int hb_knns_device_noalloc(const hb_index* h, const void* d_queries, uint64_t nq
   });
 }
 
+#ifndef HB_HOST_COPY_THREADS_DEFAULT
+#define HB_HOST_COPY_THREADS_DEFAULT 4u
+#endif
 #ifndef HB_HOST_STAGING_DEFAULT
 #define HB_HOST_STAGING_DEFAULT 1  // HB_HOST_STAGING=0 restores the cudaMemcpyAsync bracket (profiles/r02aa_host_staging_threads.log)
 #endif
@@ -429,7 +432,9 @@ class HostCopyPool {
  private:
   HostCopyPool() {
     const unsigned hw = std::thread::hardware_concurrency();
-    const int n = (int)std::min(3u, hw > 1 ? hw - 1 : 0u);
+    const char* e = std::getenv("HB_HOST_COPY_THREADS");  // threads per copy including the caller (default 4)
+    const unsigned want = e ? (unsigned)std::max(1, std::atoi(e)) : HB_HOST_COPY_THREADS_DEFAULT;
+    const int n = (int)std::min(want - 1, hw > 1 ? hw - 1 : 0u);
     for (int i = 0; i < n; ++i) helpers_.emplace_back([this] { loop(); });
     for (auto& t : helpers_) t.detach();
   }
