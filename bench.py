@@ -53,7 +53,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=10_000_000, help="data set size (default: the 10 M configuration)")
+    ap.add_argument("--n", "--rows", dest="n", type=int, default=10_000_000,
+                    help="data set size (default: the 10 M configuration); spell it --rows under torchrun, whose own parser rejects --n as ambiguous")
     ap.add_argument("--nq", type=int, default=10_000)
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--ef", type=int, default=64)
